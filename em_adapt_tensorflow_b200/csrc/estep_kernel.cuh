@@ -1,0 +1,79 @@
+// estep_kernel.cuh -- shared declarations between the E-step kernels and the C-ABI host code.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace wl {
+
+constexpr int NT = 1024;              // threads per CTA (one CTA per SM)
+constexpr int NWARPS = NT / 32;
+constexpr int HBINS = 2048;           // radix-select bins per pass
+constexpr int MAXC = 32;              // classes (label sets are 32-bit masks)
+constexpr int MAX_CLUSTER = 16;
+constexpr int TS_MAX = 33024;         // pixels per tile: one tile's terms fit in shared memory
+constexpr int STREAM_BUF_FLOATS = 21512;   // 1024 px * 21 classes + 8 floats of alignment slack
+
+// Per-image label-set description, prepared on the host (weaklabel.cpp:19-43).
+struct ImageMeta {
+    uint32_t mask;            // bit c set <=> class c present
+    int32_t P;                // number of present classes
+    int32_t first_absent;     // lowest absent class id, -1 when P == C
+    int32_t pad;
+    uint8_t plist[MAXC];      // ascending present class ids; plane p holds class plist[p]
+};
+
+// Per-cluster control block in global memory (lives in L2): merged histograms and the
+// hand-over cells of the order-exact sums.
+struct SlotCtl {
+    uint32_t hist[3][HBINS];  // rotating: pass n uses hist[n%3], zeroes hist[(n+1)%3]
+    uint32_t below[3][4];     // [n%3][0] = #keys below the bracket
+    double tot[2][MAX_CLUSTER];   // tile totals of the current round of an exact sum
+    unsigned long long carry; // running-sum bits handed from CTA to CTA
+    int32_t image;            // image this cluster is working on
+    int32_t pad[13];
+};
+
+struct EStepParams {
+    const float *map;         // scores, element (b,i,c) at map + b*s0 + i*s2 + c
+    long long s0, s2;
+    int B, N, C;
+    int num_iter, suppress;
+    float margin;
+    int nth_bg, nth_fg;       // (int)(bg*N), (int)(fg*N)   weaklabel.cpp:88
+    const ImageMeta *meta;    // [B]
+    const uint8_t *order;     // [B][num_iter][C] plane index visited at (iteration, position)
+    // per-cluster scratch
+    float *planes;            // [slots][(C+1)][Npad]: P compact class planes, last = absent max
+    uint8_t *absent_idx;      // [slots][Npad] first absent class achieving the absent max
+    SlotCtl *ctl;             // [slots]
+    int Npad, TS, ntiles, L, G;
+    int sub_px;               // pixels per streaming sub-tile
+    int *image_counter;
+    int *status;              // device-side error flag (0 = ok)
+    // outputs
+    uint8_t *labels;          // [B][N]
+    float *bias_out;          // [B][num_iter][C] by (iteration, position)
+    float *mean0;             // [B]
+    double *mean1;            // [B]
+    double *shift;            // [B]  (double)mean0 - mean1
+};
+
+size_t estep_smem_bytes();
+cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream);
+
+struct FinalizeParams {
+    float *map; long long s0, s2;
+    int B, N, C, num_iter, suppress;
+    float margin;
+    const ImageMeta *meta;
+    const uint8_t *order;
+    const float *bias;        // [B][num_iter][C]
+    const double *shift;      // [B]
+};
+cudaError_t launch_finalize_map(const FinalizeParams &p, cudaStream_t stream);
+
+cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long long n_pix, int C,
+                              int ignore_label, float *loss_mean, int *valid, float *dlogits,
+                              void *work, cudaStream_t stream, int *n_launches);
+
+}  // namespace wl

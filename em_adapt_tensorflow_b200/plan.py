@@ -1,0 +1,144 @@
+"""Device-pointer front end: EStepPlan / OrderStream over the plan API of
+include/weaklabel_cuda.h.  torch is used for device memory and streams only (tensor.data_ptr(),
+torch.cuda.current_stream()); all compute is in libweaklabel_cuda.so."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+
+class OrderStream:
+    """Explicit class-order stream == glibc rand() from `seed` (weaklabel.cpp:83)."""
+
+    def __init__(self, seed=1):
+        self._L = _lib.load()
+        self.handle = C.c_void_p(self._L.weaklabel_rng_create(seed))
+
+    def next(self):
+        return self._L.weaklabel_rng_next(self.handle)
+
+    def skip(self, n):
+        self._L.weaklabel_rng_skip(self.handle, int(n))
+
+    @property
+    def draws(self):
+        return self._L.weaklabel_rng_draws(self.handle)
+
+    def __del__(self):
+        try:
+            self._L.weaklabel_rng_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def label_set(label, num_classes):
+    """weaklabel.cpp:19-31 on a host int32 [B,H,W] ground-truth map -> uint8 [B,C]."""
+    L = _lib.load()
+    l = np.ascontiguousarray(label, dtype=np.int32)
+    B, H, W = l.shape
+    out = np.zeros((B, num_classes), np.uint8)
+    _lib.check(L.weaklabel_label_set_host(l.ctypes.data_as(C.POINTER(C.c_int)), B, H, W, num_classes,
+                                          out.ctypes.data_as(C.POINTER(C.c_ubyte))))
+    return out
+
+
+def draws_for(n_present, num_iter):
+    return _lib.load().weaklabel_draws_for(int(n_present), int(num_iter))
+
+
+class EStepPlan:
+    """One shape on one device.  prepare() fixes label sets + scalars + class order;
+    labels()/finalize_map() launch on the current torch stream and never synchronise."""
+
+    def __init__(self, B, H, W, C_, device=0):
+        self._L = _lib.load()
+        self.B, self.H, self.W, self.C, self.device = B, H, W, C_, device
+        h = C.c_void_p()
+        _lib.check(self._L.weaklabel_plan_create(C.byref(h), B, H, W, C_, device))
+        self.handle = h
+        self.num_iter = None
+
+    def tune(self, cluster_size=0, tile_pixels=0, max_clusters=0):
+        _lib.check(self._L.weaklabel_plan_tune(self.handle, cluster_size, tile_pixels, max_clusters))
+        return self
+
+    def prepare(self, present, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2,
+                rng=None):
+        p = np.ascontiguousarray(present, dtype=np.uint8)
+        assert p.shape == (self.B, self.C)
+        _lib.check(self._L.weaklabel_plan_prepare(
+            self.handle, p.ctypes.data_as(C.POINTER(C.c_ubyte)), bool(suppress_others), int(num_iter),
+            float(margin_others), float(bg), float(fg), rng.handle if rng is not None else None))
+        self.num_iter = int(num_iter)
+        return self
+
+    @staticmethod
+    def _stream():
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def labels(self, fmap, out=None):
+        """fmap: CUDA float32 tensor [B,H,W,C] (stride(3)==1, rows contiguous).  -> uint8 [B,H,W]."""
+        import torch
+        assert fmap.is_cuda and fmap.dtype == torch.float32 and tuple(fmap.shape) == (self.B, self.H, self.W, self.C)
+        assert fmap.stride(3) == 1 and fmap.stride(1) == self.W * fmap.stride(2)
+        if out is None:
+            out = torch.empty((self.B, self.H, self.W), dtype=torch.uint8, device=fmap.device)
+        _lib.check(self._L.weaklabel_estep_labels_device(self.handle, fmap.data_ptr(), fmap.stride(0),
+                                                         fmap.stride(2), out.data_ptr(), self._stream()))
+        return out
+
+    def finalize_map(self, fmap):
+        """In place: fmap becomes what the reference's e_step leaves in `map`."""
+        _lib.check(self._L.weaklabel_estep_finalize_map_device(self.handle, fmap.data_ptr(), fmap.stride(0),
+                                                               fmap.stride(2), self._stream()))
+        return fmap
+
+    def probes(self):
+        J = self.num_iter
+        order = np.full((self.B, J, self.C), -1, np.int32)
+        bias = np.zeros((self.B, J, self.C), np.float32)
+        m0 = np.zeros(self.B, np.float32)
+        m1 = np.zeros(self.B, np.float64)
+        _lib.check(self._L.weaklabel_plan_probes(
+            self.handle, order.ctypes.data_as(C.POINTER(C.c_int)), bias.ctypes.data_as(C.POINTER(C.c_float)),
+            m0.ctypes.data_as(C.POINTER(C.c_float)), m1.ctypes.data_as(C.POINTER(C.c_double))))
+        return order, bias, m0, m1
+
+    @property
+    def launches(self):
+        return self._L.weaklabel_plan_launches(self.handle)
+
+    def close(self):
+        if self.handle:
+            self._L.weaklabel_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def softmax_ce(logits, labels, ignore_label=255, want_grad=True):
+    """Fused softmax-CE forward(+backward) with ignore_label (deeplab.py:182, network.py:77-89).
+    logits CUDA float32 [..., C] contiguous, labels CUDA uint8 [...].
+    -> (loss_mean 0-d tensor, valid 0-d int32 tensor, dlogits or None)."""
+    import torch
+    L = _lib.load()
+    assert logits.is_cuda and logits.dtype == torch.float32 and logits.is_contiguous()
+    assert labels.is_cuda and labels.dtype == torch.uint8 and labels.is_contiguous()
+    Cc = logits.shape[-1]
+    n = logits.numel() // Cc
+    assert labels.numel() == n
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    valid = torch.empty((), dtype=torch.int32, device=logits.device)
+    grad = torch.empty_like(logits) if want_grad else None
+    work = torch.empty(2, dtype=torch.float64, device=logits.device)
+    _lib.check(L.weaklabel_softmax_ce_device(logits.data_ptr(), labels.data_ptr(), n, Cc, int(ignore_label),
+                                             loss.data_ptr(), valid.data_ptr(),
+                                             grad.data_ptr() if want_grad else None, work.data_ptr(),
+                                             C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return loss, valid, grad

@@ -1,0 +1,169 @@
+/*
+ * include/weaklabel_cuda.h -- C-ABI of libweaklabel_cuda.so, the B200 (sm_100a)
+ * replacement for the EM-Adapt E-step host library of xtudbxk/em-adapt-tensorflow.
+ *
+ * Every entry point is extern "C" with plain pointers and sizes; no torch types.
+ * Citations are relative to the reference tree (estep/weaklabel.cpp etc.).
+ *
+ * There is NO CPU fallback behind any of these: without a CUDA device every
+ * compute entry point fails loudly (legacy e_step: message on stderr + abort();
+ * the rest: non-zero status + weaklabel_last_error()).
+ */
+#ifndef WEAKLABEL_CUDA_H
+#define WEAKLABEL_CUDA_H
+
+#include <stdbool.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define WL_API __attribute__((visibility("default")))
+#else
+#define WL_API
+#endif
+
+#define WEAKLABEL_MAX_CLASSES 32     /* label sets are 32-bit masks                  */
+#define WEAKLABEL_OK 0
+#define WEAKLABEL_ERR_CUDA 1         /* a CUDA runtime call or kernel failed         */
+#define WEAKLABEL_ERR_ARG 2          /* bad shape / stride / parameter               */
+#define WEAKLABEL_ERR_EMPTY_SET 3    /* an image has no class < C at even coordinates
+                                        (the reference runs off its array there,
+                                        weaklabel.cpp:83 with present_label_num==0)  */
+#define WEAKLABEL_ERR_STATE 4        /* plan used before weaklabel_plan_prepare      */
+
+/* ---------------------------------------------------------------------------
+ * 1. Drop-in legacy entry point.  Replaces estep/weaklabel.cpp:6-7 exactly:
+ *    same symbol, same argument order and types, same in-place contract, and it
+ *    returns `map`.  Bound by the reference's ctypes callers without change
+ *    (estep.py:15,30; estep/estep.py:16,31; estep/estep_with_ctype.py:17,22).
+ *
+ *    map    float32, logical [B,H,W,C], HOST memory, mutated in place; element
+ *           (b,i,c) at map + b*stride[0]/4 + i*stride[2]/4 + c (weaklabel.cpp:50)
+ *    shape  {B,H,W,C}; stride = BYTE strides (weaklabel.cpp:13-16)
+ *    label  int32 dense [B,H,W] ground-truth map; the image-level label set is
+ *           its stride-2 scan, values >= C are void (weaklabel.cpp:19-31)
+ *    Class order: std::random_shuffle on the process-global libc rand(), one
+ *    image after the other (weaklabel.cpp:83) -- this library consumes the very
+ *    same rand() stream, max(P-2,0) draws per iteration per image.
+ *    Batch > 1 (which crashes in the reference, weaklabel.cpp:117-118) is
+ *    defined as B consecutive single-image calls in index order.
+ *    Errors cannot be reported through this signature: they print to stderr
+ *    and abort().
+ * ------------------------------------------------------------------------- */
+WL_API float *e_step(float *map, const int *shape, const int *stride, const int *label,
+              const bool suppress_others, const int num_iter, const float margin_others,
+              float bg, float fg);
+
+/* ---------------------------------------------------------------------------
+ * 2. Status.
+ * ------------------------------------------------------------------------- */
+WL_API const char *weaklabel_last_error(void);   /* thread-local, "" when none            */
+WL_API int weaklabel_version(void);              /* 10000*major + 100*minor + patch       */
+WL_API int weaklabel_device_count(void);         /* 0 when no CUDA device is usable       */
+
+/* ---------------------------------------------------------------------------
+ * 3. Explicit class-order stream.  The reference's only hidden state is the
+ *    glibc rand() stream behind std::random_shuffle (weaklabel.cpp:83); this
+ *    object reproduces that generator bit-for-bit from a seed so that a run is
+ *    reproducible and shardable (srand(1) == process start).
+ * ------------------------------------------------------------------------- */
+typedef struct weaklabel_rng weaklabel_rng;
+WL_API weaklabel_rng *weaklabel_rng_create(unsigned int seed);
+WL_API void weaklabel_rng_destroy(weaklabel_rng *rng);
+WL_API int weaklabel_rng_next(weaklabel_rng *rng);              /* == rand()             */
+WL_API void weaklabel_rng_skip(weaklabel_rng *rng, long long n_draws);
+WL_API long long weaklabel_rng_draws(const weaklabel_rng *rng); /* draws since seeding   */
+/* draws one image's E-step consumes: num_iter * max(P-2, 0) */
+WL_API long long weaklabel_draws_for(int n_present, int num_iter);
+
+/* ---------------------------------------------------------------------------
+ * 4. Image-level label sets (weaklabel.cpp:19-31): stride-2 scan of a dense
+ *    int32 [B,H,W] HOST ground-truth map into a 0/1 matrix [B][C].
+ * ------------------------------------------------------------------------- */
+WL_API int weaklabel_label_set_host(const int *label, int B, int H, int W, int C,
+                             unsigned char *present /* [B][C] out */);
+
+/* ---------------------------------------------------------------------------
+ * 5. Device-resident E-step.  A plan owns the scratch (compact class planes,
+ *    histograms) for one shape on one device; prepare() fixes the label sets,
+ *    the five scalars of weaklabel.cpp:7 and the class order; run() only
+ *    launches kernels on `stream` (a cudaStream_t passed as void*), never
+ *    synchronises, and takes raw DEVICE pointers.
+ *
+ *    Algorithm per image (weaklabel.cpp:35-112): absent-class suppression,
+ *    floored per-pixel max, num_iter x P exact order-statistic biases
+ *    (std::nth_element's value), re-centring by (mean_max_0 - mean_max_1) with
+ *    the reference's sequential float / double summation order, then
+ *    argmax over all C classes, lowest index on ties (deeplab.py:123).
+ * ------------------------------------------------------------------------- */
+typedef struct weaklabel_plan weaklabel_plan;
+
+WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, int W, int C, int device);
+WL_API void weaklabel_plan_destroy(weaklabel_plan *plan);
+
+/* present: [B][C] 0/1 (from weaklabel_label_set_host or the caller's image-level
+ * labels).  rng == NULL draws the class order from the process-global libc
+ * rand() exactly as the reference would; otherwise from the explicit stream. */
+WL_API int weaklabel_plan_prepare(weaklabel_plan *plan, const unsigned char *present,
+                           bool suppress_others, int num_iter, float margin_others,
+                           float bg, float fg, weaklabel_rng *rng);
+
+/* d_map: const float32 scores, element (b,i,c) at d_map + b*batch_stride +
+ * i*pixel_stride + c (ELEMENT strides; contiguous NHWC: H*W*C and C).
+ * d_labels: uint8 [B][H*W] out.  The score map is NOT modified. */
+WL_API int weaklabel_estep_labels_device(weaklabel_plan *plan, const float *d_map,
+                                  long long batch_stride, long long pixel_stride,
+                                  unsigned char *d_labels, void *stream);
+
+/* The reference's in-place contract on DEVICE memory: d_map becomes the
+ * bias-shifted, re-centred score map (what e_step leaves in `map`).  Must be
+ * called after weaklabel_estep_labels_device on the same (unmodified) d_map;
+ * d_labels of that call may be NULL if only the map is wanted. */
+WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *plan, float *d_map,
+                                        long long batch_stride, long long pixel_stride,
+                                        void *stream);
+
+/* Probes for parity tests (host copies; synchronises the plan's last stream):
+ * order/bias [B][num_iter][C] indexed (iteration, visit position) with -1 / 0
+ * padding, mean0 [B] float, mean1 [B] double.  Any pointer may be NULL. */
+WL_API int weaklabel_plan_probes(weaklabel_plan *plan, int *order, float *bias,
+                          float *mean0, double *mean1);
+
+/* tuning knobs, mostly for tests: cluster size (0 = auto; 1,2,4,8,16),
+ * tile size in pixels (0 = auto), number of resident clusters (0 = auto). */
+WL_API int weaklabel_plan_tune(weaklabel_plan *plan, int cluster_size, int tile_pixels,
+                        int max_clusters);
+/* kernels launched by this plan since creation (bench.py's gpu_launches) */
+WL_API long long weaklabel_plan_launches(const weaklabel_plan *plan);
+
+/* One-call convenience over a cached plan: host GT label map, device scores.
+ * d_map_out may be NULL (labels only) or == a writable copy target of d_map's
+ * layout that receives the shifted map.  rng as in weaklabel_plan_prepare. */
+WL_API int e_step_labels_device(const float *d_map, const int *shape, const int *stride_bytes,
+                         const int *h_label, bool suppress_others, int num_iter,
+                         float margin_others, float bg, float fg, weaklabel_rng *rng,
+                         unsigned char *d_labels, float *d_map_out, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * 6. Fused softmax cross-entropy, forward + backward, ignore_label (255).
+ *    Replaces deeplab.py:182 (tf.nn.sparse_softmax_cross_entropy_with_logits +
+ *    reduce_mean) with the ignore semantics of network.py:77-89: pixels whose
+ *    label == ignore_label or >= C contribute no loss, no gradient, and are
+ *    left out of the mean's denominator.
+ *    d_logits [n_pix][C] float32 (pre-E-step fc8 scores), d_labels [n_pix] uint8,
+ *    d_loss_mean: 1 float out, d_valid: 1 int out (kept pixels),
+ *    d_dlogits [n_pix][C] out = (softmax - onehot) / valid, or NULL (forward only).
+ *    d_work: >= 16 bytes of device scratch (zeroed by the call).
+ * ------------------------------------------------------------------------- */
+WL_API int weaklabel_softmax_ce_device(const float *d_logits, const unsigned char *d_labels,
+                                long long n_pix, int C, int ignore_label,
+                                float *d_loss_mean, int *d_valid, float *d_dlogits,
+                                void *d_work, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WEAKLABEL_CUDA_H */
