@@ -128,6 +128,37 @@ extern "C" WL_API int weaklabel_label_set_host(const int *label, int B, int H, i
     return WEAKLABEL_OK;
 }
 
+// Class visiting order (weaklabel.cpp:36-43, 83) for B consecutive images on one stream:
+// order[b][j][t] = class id visited at position t of iteration j, -1 padded.
+// std::random_shuffle(label_single+1, label_single+P) is, in libstdc++ (bits/stl_algo.h),
+// "for i = 1..n-1: swap(a[i], a[rand() % (i+1)])" on the n = P-1 tail entries; the permutation
+// carries over from iteration to iteration and the first entry never moves.
+extern "C" WL_API int weaklabel_draw_order_host(const unsigned char *present, int B, int C, int num_iter,
+                                         weaklabel_rng *rng, int *order) {
+    if (!present || !order || B < 0 || C <= 0 || C > WEAKLABEL_MAX_CLASSES || num_iter < 0)
+        return fail(WEAKLABEL_ERR_ARG, "weaklabel_draw_order_host: bad argument");
+    int cls[WEAKLABEL_MAX_CLASSES];
+    for (int b = 0; b < B; b++) {
+        int P = 0;
+        for (int c = 0; c < C; c++)
+            if (present[(size_t)b * C + c]) cls[P++] = c;
+        if (P == 0)
+            return fail(WEAKLABEL_ERR_EMPTY_SET, "image %d has an empty label set (the reference "
+                        "crashes there, weaklabel.cpp:83)", b);
+        for (int j = 0; j < num_iter; j++) {
+            int *tail = cls + 1;
+            const int n = P - 1;
+            for (int i = 1; i < n; i++) {
+                const int r = draw(rng) % (i + 1);
+                if (r != i) { const int t = tail[i]; tail[i] = tail[r]; tail[r] = t; }
+            }
+            int *o = order + ((size_t)b * num_iter + j) * C;
+            for (int t = 0; t < C; t++) o[t] = t < P ? cls[t] : -1;
+        }
+    }
+    return WEAKLABEL_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // plans
 // ---------------------------------------------------------------------------------------------
@@ -285,7 +316,10 @@ extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned 
     }
     pl->h_meta.assign(B, ImageMeta());
     pl->h_order.assign((size_t)B * num_iter * C, 0);
-    int cls[WEAKLABEL_MAX_CLASSES], pos_of[WEAKLABEL_MAX_CLASSES];
+    std::vector<int> ord_cls((size_t)B * num_iter * C + 1, -1);
+    int rc0 = weaklabel_draw_order_host(present, B, C, num_iter, rng, ord_cls.data());
+    if (rc0) return rc0;
+    int pos_of[WEAKLABEL_MAX_CLASSES];
     for (int b = 0; b < B; b++) {
         ImageMeta &m = pl->h_meta[b];
         memset(&m, 0, sizeof m);
@@ -295,26 +329,17 @@ extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned 
             if (present[(size_t)b * C + c]) {
                 m.mask |= 1u << c;
                 m.plist[P] = (uint8_t)c;
-                pos_of[c] = P;
-                cls[P++] = c;
+                pos_of[c] = P++;
             } else if (m.first_absent < 0) {
                 m.first_absent = c;
             }
         }
         m.P = P;
-        // weaklabel.cpp:83 -- std::random_shuffle(label_single+1, label_single+P): for
-        // i = 1..n-1 swap a[i], a[rand() % (i+1)] on the tail; the permutation carries over
-        // from iteration to iteration, the first entry never moves.
-        for (int j = 0; j < num_iter; j++) {
-            int *tail = cls + 1;
-            const int n = P - 1;
-            for (int i = 1; i < n; i++) {
-                const int r = draw(rng) % (i + 1);
-                if (r != i) { const int t = tail[i]; tail[i] = tail[r]; tail[r] = t; }
+        for (int j = 0; j < num_iter; j++)
+            for (int t = 0; t < P; t++) {
+                const size_t o = ((size_t)b * num_iter + j) * C + t;
+                pl->h_order[o] = (uint8_t)pos_of[ord_cls[o]];
             }
-            for (int t = 0; t < P; t++)
-                pl->h_order[((size_t)b * num_iter + j) * C + t] = (uint8_t)pos_of[cls[t]];
-        }
     }
     CUDA_TRY(cudaSetDevice(pl->device));
     if (pl->last_stream) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));   // tables may be in use

@@ -86,6 +86,14 @@ WL_API long long weaklabel_draws_for(int n_present, int num_iter);
 WL_API int weaklabel_label_set_host(const int *label, int B, int H, int W, int C,
                              unsigned char *present /* [B][C] out */);
 
+/* Class visiting order of B consecutive images on one stream (weaklabel.cpp:36-43, 83):
+ * order [B][num_iter][C] = class id at (iteration, visit position), -1 padded.
+ * Pure host code; rng == NULL uses the process-global libc rand().  This is the table
+ * weaklabel_plan_prepare uploads; exposed so that image shards can be checked and
+ * positioned (weaklabel_rng_skip) without a device. */
+WL_API int weaklabel_draw_order_host(const unsigned char *present, int B, int C, int num_iter,
+                              weaklabel_rng *rng, int *order);
+
 /* ---------------------------------------------------------------------------
  * 5. Device-resident E-step.  A plan owns the scratch (compact class planes,
  *    histograms) for one shape on one device; prepare() fixes the label sets,
