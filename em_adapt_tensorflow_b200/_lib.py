@@ -51,6 +51,7 @@ def load():
     L.weaklabel_draws_for.argtypes = [C.c_int, C.c_int]
     L.weaklabel_draws_for.restype = C.c_longlong
     L.weaklabel_label_set_host.argtypes = [_i32p, C.c_int, C.c_int, C.c_int, C.c_int, _u8p]
+    L.weaklabel_draw_order_host.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_void_p, _i32p]
     L.weaklabel_plan_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     L.weaklabel_plan_destroy.argtypes = [C.c_void_p]
     L.weaklabel_plan_destroy.restype = None
@@ -80,7 +81,7 @@ def check(rc):
 EXPORTS = ["e_step", "e_step_labels_device", "weaklabel_last_error", "weaklabel_version",
            "weaklabel_device_count", "weaklabel_rng_create", "weaklabel_rng_destroy",
            "weaklabel_rng_next", "weaklabel_rng_skip", "weaklabel_rng_draws", "weaklabel_draws_for",
-           "weaklabel_label_set_host", "weaklabel_plan_create", "weaklabel_plan_destroy",
+           "weaklabel_label_set_host", "weaklabel_draw_order_host", "weaklabel_plan_create", "weaklabel_plan_destroy",
            "weaklabel_plan_prepare", "weaklabel_estep_labels_device",
            "weaklabel_estep_finalize_map_device", "weaklabel_plan_probes", "weaklabel_plan_tune",
            "weaklabel_plan_launches", "weaklabel_softmax_ce_device"]
