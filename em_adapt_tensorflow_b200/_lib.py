@@ -63,6 +63,8 @@ def load():
                                                       C.c_longlong, C.c_void_p]
     L.weaklabel_plan_probes.argtypes = [C.c_void_p, _i32p, _f32p, _f32p, C.POINTER(C.c_double)]
     L.weaklabel_plan_tune.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+    L.weaklabel_plan_set_path.argtypes = [C.c_void_p, C.c_int]
+    L.weaklabel_plan_last_path.argtypes = [C.c_void_p]
     L.weaklabel_plan_launches.argtypes = [C.c_void_p]
     L.weaklabel_plan_launches.restype = C.c_longlong
     L.e_step_labels_device.argtypes = [C.c_void_p, _i32p, _i32p, _i32p, C.c_bool, C.c_int, C.c_float,
@@ -84,4 +86,5 @@ EXPORTS = ["e_step", "e_step_labels_device", "weaklabel_last_error", "weaklabel_
            "weaklabel_label_set_host", "weaklabel_draw_order_host", "weaklabel_plan_create", "weaklabel_plan_destroy",
            "weaklabel_plan_prepare", "weaklabel_estep_labels_device",
            "weaklabel_estep_finalize_map_device", "weaklabel_plan_probes", "weaklabel_plan_tune",
-           "weaklabel_plan_launches", "weaklabel_softmax_ce_device"]
+           "weaklabel_plan_launches", "weaklabel_plan_set_path", "weaklabel_plan_last_path",
+           "weaklabel_softmax_ce_device"]

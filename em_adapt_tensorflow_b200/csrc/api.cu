@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -14,9 +15,6 @@
 #include "../../include/weaklabel_cuda.h"
 #include "estep_kernel.cuh"
 
-namespace wl {
-int estep_max_clusters(int G);
-}
 
 using namespace wl;
 
@@ -164,9 +162,13 @@ extern "C" WL_API int weaklabel_draw_order_host(const unsigned char *present, in
 // ---------------------------------------------------------------------------------------------
 struct weaklabel_plan {
     int B, H, W, C, N, device, sms;
-    int G, TS, ntiles, L, Npad, slots, sub_px;
-    int tune_G, tune_TS, tune_slots;
+    int G, TS, ntiles, L, Npad, slots, sub_px;      // generic kernel (estep_kernel.cu)
+    int fG, fTS, fL, fslots;                        // on-chip fast path (estep_fast.cu); fG == 0: unavailable
+    int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 fast
     bool geometry_ok;
+    int scratch_slots;
+    int *d_sched;
+    int last_path;
     float *d_planes;
     uint8_t *d_absidx;
     SlotCtl *d_ctl;
@@ -229,9 +231,42 @@ static int plan_geometry(weaklabel_plan *pl) {
     if (slots > pl->B) slots = pl->B;
     if (slots < 1) slots = 1;
     pl->slots = slots;
-    CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)slots * (pl->C + 1) * pl->Npad * sizeof(float)));
-    CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)slots * pl->Npad));
-    CUDA_TRY(cudaMalloc(&pl->d_ctl, (size_t)slots * sizeof(SlotCtl)));
+    // fast path: one tile of at most FAST_PPT_MAX*NT pixels per CTA, so the cluster must be large
+    // enough to hold the image; small batches take larger clusters to fill the device
+    pl->fG = 0;
+    {
+        const int cap = FAST_PPT_MAX * NT;
+        int fG = pl->tune_G;
+        if (fG == 0) {
+            fG = 1;
+            while (fG < MAX_CLUSTER && (N + fG - 1) / fG > cap) fG *= 2;
+            while (fG < 8 && (long long)pl->B * fG * 2 <= pl->sms && N / (2 * fG) >= 4096) fG *= 2;
+        }
+        int fTS = pl->tune_TS ? pl->tune_TS : (N + fG - 1) / fG;
+        fTS = (fTS + 3) / 4 * 4;
+        if (fTS < 4) fTS = 4;
+        if (fTS <= cap && (long long)fTS * fG >= N && fast_ppt_for(fTS) > 0) {
+            int fmax = estep_fast_max_clusters(fG, fTS);
+            if (fmax > 0) {
+                int fs = pl->tune_slots ? pl->tune_slots : fmax;
+                if (fs > fmax) fs = fmax;
+                if (fs > pl->B) fs = pl->B;
+                if (fs < 1) fs = 1;
+                pl->fG = fG; pl->fTS = fTS; pl->fslots = fs;
+                pl->fL = (fTS + NT - 1) / NT;
+                if (pl->fL % 2 == 0) pl->fL++;
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
+    if (pl->tune_path == 2 && pl->fG == 0)
+        return fail(WEAKLABEL_ERR_ARG, "the fast path cannot hold %d pixels with this cluster/tile tuning", N);
+    const int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
+    pl->scratch_slots = ss;
+    CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 1) * pl->Npad * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)ss * pl->Npad));
+    CUDA_TRY(cudaMalloc(&pl->d_ctl, (size_t)ss * sizeof(SlotCtl)));
     pl->geometry_ok = true;
     return WEAKLABEL_OK;
 }
@@ -264,6 +299,7 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean0, (size_t)B * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean1, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_shift, (size_t)B * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_sched, (size_t)B * sizeof(int));
     if (e != cudaSuccess) {
         weaklabel_plan_destroy(pl);
         return fail(WEAKLABEL_ERR_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
@@ -277,7 +313,7 @@ extern "C" WL_API void weaklabel_plan_destroy(weaklabel_plan *pl) {
     cudaSetDevice(pl->device);
     plan_free_geometry(pl);
     cudaFree(pl->d_counter); cudaFree(pl->d_meta); cudaFree(pl->d_order); cudaFree(pl->d_bias);
-    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift);
+    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift); cudaFree(pl->d_sched);
     delete pl;
 }
 
@@ -293,6 +329,13 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
 }
 
 extern "C" WL_API long long weaklabel_plan_launches(const weaklabel_plan *pl) { return pl ? pl->launches : 0; }
+
+extern "C" WL_API int weaklabel_plan_set_path(weaklabel_plan *pl, int path) {
+    if (!pl || path < 0 || path > 2) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic) or 2 (fast)");
+    pl->tune_path = path;
+    return WEAKLABEL_OK;
+}
+extern "C" WL_API int weaklabel_plan_last_path(const weaklabel_plan *pl) { return pl ? pl->last_path : 0; }
 
 extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned char *present,
                                       bool suppress_others, int num_iter, float margin_others,
@@ -351,6 +394,13 @@ extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned 
         CUDA_TRY(cudaMalloc(&pl->d_bias, osz * sizeof(float)));
         pl->order_cap = osz;
     }
+    {   // claim order: largest label sets first (longest jobs first keeps the tail short)
+        std::vector<int> sched(B);
+        for (int b = 0; b < B; b++) sched[b] = b;
+        std::stable_sort(sched.begin(), sched.end(),
+                         [&](int a, int b2) { return pl->h_meta[a].P > pl->h_meta[b2].P; });
+        CUDA_TRY(cudaMemcpy(pl->d_sched, sched.data(), (size_t)B * sizeof(int), cudaMemcpyHostToDevice));
+    }
     CUDA_TRY(cudaMemcpy(pl->d_meta, pl->h_meta.data(), (size_t)B * sizeof(ImageMeta), cudaMemcpyHostToDevice));
     if (!pl->h_order.empty())
         CUDA_TRY(cudaMemcpy(pl->d_order, pl->h_order.data(), pl->h_order.size(), cudaMemcpyHostToDevice));
@@ -384,14 +434,30 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.nth_bg = pl->nth_bg; p.nth_fg = pl->nth_fg;
     p.meta = pl->d_meta; p.order = pl->d_order;
     p.planes = pl->d_planes; p.absent_idx = pl->d_absidx; p.ctl = pl->d_ctl;
-    p.Npad = pl->Npad; p.TS = pl->TS; p.ntiles = pl->ntiles; p.L = pl->L; p.G = pl->G;
-    p.sub_px = pl->sub_px;
+    // the on-chip fast path covers suppress_others with a margin >= 0 on contiguous pixels
+    // (weaklabel.cpp:45-65 then guarantees that no absent class exceeds a present one)
+    const bool fast_ok = pl->fG > 0 && pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
+    if (pl->tune_path == 2 && !fast_ok)
+        return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
+                    "contiguous pixels)");
+    const bool fast = fast_ok && pl->tune_path != 1;
+    int slots_used = pl->slots;
+    p.Npad = pl->Npad; p.sub_px = pl->sub_px;
+    if (fast) {
+        p.TS = pl->fTS; p.ntiles = (pl->N + pl->fTS - 1) / pl->fTS; p.L = pl->fL; p.G = pl->fG;
+        slots_used = pl->fslots;
+    } else {
+        p.TS = pl->TS; p.ntiles = pl->ntiles; p.L = pl->L; p.G = pl->G;
+    }
+    p.sched = pl->d_sched;
     p.image_counter = pl->d_counter; p.status = pl->d_counter + 1;
     p.labels = d_labels; p.bias_out = pl->d_bias;
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
     CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
-    CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)pl->slots * sizeof(SlotCtl), st));
-    CUDA_TRY(launch_estep(p, pl->slots, st));
+    CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
+    if (fast) CUDA_TRY(launch_estep_fast(p, slots_used, st));
+    else CUDA_TRY(launch_estep(p, slots_used, st));
+    pl->last_path = fast ? 2 : 1;
     pl->launches += 1;
     pl->last_stream = st;
     return WEAKLABEL_OK;

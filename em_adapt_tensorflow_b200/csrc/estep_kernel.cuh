@@ -49,6 +49,7 @@ struct EStepParams {
     int Npad, TS, ntiles, L, G;
     int sub_px;               // pixels per streaming sub-tile
     int *image_counter;
+    const int *sched;         // [B] order in which images are claimed (largest label sets first), or NULL
     int *status;              // device-side error flag (0 = ok)
     // outputs
     uint8_t *labels;          // [B][N]
@@ -60,6 +61,14 @@ struct EStepParams {
 
 size_t estep_smem_bytes();
 cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream);
+int estep_max_clusters(int G);
+
+// on-chip fast path (estep_fast.cu): one tile of at most FAST_PPT_MAX * NT pixels per CTA
+constexpr int FAST_PPT_SMALL = 4;
+constexpr int FAST_PPT_MAX = 33;
+int fast_ppt_for(int tile_pixels);                     // 0 when the tile does not fit
+cudaError_t launch_estep_fast(const EStepParams &p, int n_clusters, cudaStream_t stream);
+int estep_fast_max_clusters(int G, int tile_pixels);
 
 struct FinalizeParams {
     float *map; long long s0, s2;

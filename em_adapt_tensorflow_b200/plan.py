@@ -63,6 +63,15 @@ class EStepPlan:
         _lib.check(self._L.weaklabel_plan_tune(self.handle, cluster_size, tile_pixels, max_clusters))
         return self
 
+    def set_path(self, path):
+        """0 auto, 1 generic kernel, 2 on-chip fast path (labels() fails if it does not apply)."""
+        _lib.check(self._L.weaklabel_plan_set_path(self.handle, {"auto": 0, "generic": 1, "fast": 2}.get(path, path)))
+        return self
+
+    @property
+    def last_path(self):
+        return {0: None, 1: "generic", 2: "fast"}[self._L.weaklabel_plan_last_path(self.handle)]
+
     def prepare(self, present, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2,
                 rng=None):
         p = np.ascontiguousarray(present, dtype=np.uint8)

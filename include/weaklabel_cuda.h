@@ -144,6 +144,12 @@ WL_API int weaklabel_plan_probes(weaklabel_plan *plan, int *order, float *bias,
  * tile size in pixels (0 = auto), number of resident clusters (0 = auto). */
 WL_API int weaklabel_plan_tune(weaklabel_plan *plan, int cluster_size, int tile_pixels,
                         int max_clusters);
+/* Two kernels implement the E-step: the on-chip fast path (suppress_others with a margin
+ * >= 0, contiguous pixels, image fits the cluster) and the generic one (everything else).
+ * path: 0 = choose automatically (default), 1 = force generic, 2 = force fast (run() fails if
+ * it does not apply).  weaklabel_plan_last_path: which one the last run() launched. */
+WL_API int weaklabel_plan_set_path(weaklabel_plan *plan, int path);
+WL_API int weaklabel_plan_last_path(const weaklabel_plan *plan);
 /* kernels launched by this plan since creation (bench.py's gpu_launches) */
 WL_API long long weaklabel_plan_launches(const weaklabel_plan *plan);
 

@@ -193,6 +193,8 @@ CASES = [
     _case("rank_last", 1, 41, 41, seed=126, sets=[[0, 8]], bg=0.9999, fg=0.9999),
     _case("defaults_py", 1, 41, 41, seed=127, sets=[[0, 1, 2]], bg=0.5, fg=0.25),
     _case("margin_big", 1, 41, 41, seed=128, sets=[[0, 6]], margin_others=0.5),
+    # a negative margin lifts suppressed absent classes ABOVE the smallest present one
+    _case("margin_neg", 2, 41, 41, seed=138, sets=[[0, 6, 11], [4]], margin_others=-0.75, store="full"),
     # (12) magnitudes
     _case("mag_big", 2, 41, 41, kind="big", seed=129, sets=[[0, 9], [0, 3, 5]]),
     _case("mag_big_p1", 1, 41, 41, kind="big", seed=130, sets=[[7]], store="full"),

@@ -28,19 +28,28 @@ def _oracle_run(f, l, p):
     return fo, orc.argmax_labels(fo), probes
 
 
-def _device_run(f, l, p, tune=None, want_map=True):
+def _fast_applies(p):
+    return bool(p["suppress_others"]) and p["margin_others"] >= 0
+
+
+def _device_run(f, l, p, tune=None, want_map=True, path="auto"):
     torch = _torch()
     B, H, W, C = f.shape
     t = torch.from_numpy(np.ascontiguousarray(f)).cuda()
     plan = wl.EStepPlan(B, H, W, C)
     if tune:
         plan.tune(*tune)
+    plan.set_path(path)
     plan.prepare(wl.label_set(l, C), p["suppress_others"], p["num_iter"], p["margin_others"], p["bg"], p["fg"],
                  rng=wl.OrderStream(1))
     lab = plan.labels(t)
     torch.cuda.synchronize()
     assert t.cpu().numpy().tobytes() == np.ascontiguousarray(f).tobytes(), "labels() must not modify the map"
     probes = plan.probes()
+    if path == "auto" and tune is None:
+        assert plan.last_path == ("fast" if _fast_applies(p) else "generic")
+    elif path != "auto":
+        assert plan.last_path == path
     fm = None
     if want_map:
         plan.finalize_map(t)
@@ -49,12 +58,14 @@ def _device_run(f, l, p, tune=None, want_map=True):
     return fm, lab.cpu().numpy(), probes
 
 
+@pytest.mark.parametrize("path", ["auto", "generic"])
 @pytest.mark.parametrize("name", ALL)
-def test_device_api_bit_exact(name, golden):
+def test_device_api_bit_exact(name, path, golden):
+    """path auto = the on-chip fast kernel wherever it applies; generic = estep_kernel.cu."""
     meta, arrays = golden
     f, l, p = cases.build_case(name)
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
-    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p)
+    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, path=path)
     assert np.array_equal(order_g, order_o)
     assert bias_g.tobytes() == bias_o.tobytes()
     assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
@@ -109,14 +120,47 @@ TUNES = [(1, 64, 0), (2, 64, 0), (4, 128, 0), (8, 32, 2), (2, 0, 0), (16, 16, 0)
 @pytest.mark.parametrize("name", ["c1_41_p2", "p5_seq3", "nosuppress_p3", "p21_41", "allneg_p3", "ties_int",
                                   "shape_7x5", "mag_big"])
 def test_forced_geometries(name, tune):
-    """Cluster sizes 1..16, multi-tile and multi-round geometries give the same bits."""
+    """Generic kernel: cluster sizes 1..16, multi-tile and multi-round geometries give the same bits."""
     f, l, p = cases.build_case(name)
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
-    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune)
+    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="generic")
     assert bias_g.tobytes() == bias_o.tobytes()
     assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
     assert np.array_equal(got_lab, want_lab)
     assert got_map.tobytes() == want_map.tobytes()
+
+
+FAST_TUNES = [(1, 0, 0), (2, 0, 0), (4, 0, 0), (8, 0, 1), (16, 0, 0), (2, 1200, 0), (1, 4100, 0), (2, 5000, 2)]
+
+
+@pytest.mark.parametrize("tune", FAST_TUNES)
+@pytest.mark.parametrize("name", ["c1_41_p2", "p5_seq3", "p21_41", "allneg_p3", "ties_int", "ties_const", "shape_7x5",
+                                  "shape_1x1", "mag_big", "mag_tiny", "rank_last", "c2_41_b30", "shape_100x37"])
+def test_fast_path_forced_geometries(name, tune):
+    """On-chip fast kernel: cluster sizes 1..16 (DSMEM exchange), tiles larger than the image
+    (idle CTAs), both per-thread pixel counts (tile > 4096 pixels selects the 33-pixel build)."""
+    f, l, p = cases.build_case(name)
+    N = f.shape[1] * f.shape[2]
+    G, TS, _ = tune
+    if TS and G * TS < N:
+        pytest.skip("tile tuning does not hold the image")
+    want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
+    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="fast")
+    assert bias_g.tobytes() == bias_o.tobytes()
+    assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
+    assert np.array_equal(got_lab, want_lab)
+    assert got_map.tobytes() == want_map.tobytes()
+
+
+def test_fast_path_refuses_what_it_does_not_cover():
+    torch = _torch()
+    f, l, p = cases.build_case("nosuppress_p3")
+    plan = wl.EStepPlan(*f.shape)
+    plan.set_path("fast")
+    plan.prepare(wl.label_set(l, 21), suppress_others=False, rng=wl.OrderStream(1))
+    with pytest.raises(wl.WeakLabelError):
+        plan.labels(torch.from_numpy(np.ascontiguousarray(f)).cuda())
+    plan.close()
 
 
 def test_one_call_device_entry_and_repeatability():
@@ -209,8 +253,9 @@ def test_full_size_properties():
     t2 = t.clone()
     plan.finalize_map(t2)
     assert torch.equal(t2.argmax(dim=3).to(torch.uint8), lab)
-    mx = t2.amax(dim=3).double().mean(dim=(1, 2)).cpu().numpy()
-    assert np.allclose(mx, m0.astype(np.float64), rtol=0, atol=1e-4)
+    shift = torch.from_numpy(m0.astype(np.float64) - m1).cuda().view(B, 1, 1)
+    floored = (t2.amax(dim=3).double() - shift).clamp_min(float(np.finfo(np.float32).tiny))
+    assert np.allclose(floored.mean(dim=(1, 2)).cpu().numpy(), m1, rtol=0, atol=1e-4)
     plan.close()
 
 

@@ -8,8 +8,11 @@ case $what in
 tests)
   timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
   tail -5 gpurun_out/pytest_gpu.log ;;
+testsall)
+  timeout 1200 python -m pytest tests -q -m gpu -x --timeout 120 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
+  grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/pytest_gpu.log | head -60 ;;
 smoke)
-  timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" | tee -a gpurun_out/smoke.log; tail -3 gpurun_out/smoke.log ;;
+  timeout 200 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" | tee -a gpurun_out/smoke.log; tail -3 gpurun_out/smoke.log ;;
 micro)
   timeout 300 ./tools/microbench > gpurun_out/microbench.txt 2>&1; echo "micro exit $?"; cat gpurun_out/microbench.txt ;;
 bench)
