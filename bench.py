@@ -222,6 +222,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--parity-images", type=int, default=8)
     ap.add_argument("--tune", default="", help="cluster,tile,clusters for weaklabel_plan_tune")
+    ap.add_argument("--threads", type=int, default=0, help="threads per CTA of the fast kernel (0 auto, 512, 1024)")
+    ap.add_argument("--path", default="auto", help="auto | generic | fast | fast1")
+    ap.add_argument("--phase-profile", default="", help="write per-image phase stamps of one extra run to this .npy")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -270,6 +273,10 @@ def main():
     plan = wl.EStepPlan(B, H, W, C, device=local_rank)
     if args.tune:
         plan.tune(*[int(x) for x in args.tune.split(",")])
+    if args.threads:
+        plan.set_threads(args.threads)
+    if args.path != "auto":
+        plan.set_path(args.path)
     stream = wl.positioned_stream(present_all, PARAMS["num_iter"], lo)
     plan.prepare(present, PARAMS["suppress_others"], PARAMS["num_iter"], PARAMS["margin_others"],
                  PARAMS["bg"], PARAMS["fg"], rng=stream)
@@ -299,6 +306,12 @@ def main():
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     max_ms = float(t.item())
+
+    if args.phase_profile and rank == 0:
+        plan.profile(True)
+        plan.labels(fmap, out=labels)
+        torch.cuda.synchronize()
+        np.save(args.phase_profile, plan.profile(False, read=True))
 
     # ---- parity gate: first images of the shard against the oracle (checker only) ----
     parity = None
@@ -359,7 +372,7 @@ def main():
                                 l2="inputs 5.66 GB per GPU >> 126 MB L2 (no flush needed)",
                                 parallelism="image-sharded x%d, no collective" % world),
                     roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                                  traffic=ncu_traffic(), kernel="estep_cluster_kernel",
+                                  traffic=ncu_traffic(), kernel={"fast": "estep_v2_kernel", "fast1": "estep_fast_kernel", "generic": "estep_cluster_kernel"}.get(plan.last_path, "?"),
                                   alg_bytes_per_pixel=ALG_BYTES_PER_PIXEL, kernel_ms=k_ms, peak_source=peak_src),
                     cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clocks, parity=parity)
         print(json.dumps(line), flush=True)

@@ -164,7 +164,10 @@ struct weaklabel_plan {
     int B, H, W, C, N, device, sms;
     int G, TS, ntiles, L, Npad, slots, sub_px;      // generic kernel (estep_kernel.cu)
     int fG, fTS, fL, fslots;                        // on-chip fast path (estep_fast.cu); fG == 0: unavailable
-    int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 fast
+    int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 fast (v2), 3 first-generation fast
+    int tune_nt;                                    // v2 threads per CTA (0 auto, 512, 1024)
+    V2Config v2; bool v2_ok; int v2_slots;          // second-generation kernel (estep_v2.cu)
+    unsigned long long *d_prof; bool prof_on;       // [B][8] phase time stamps
     bool geometry_ok;
     int scratch_slots;
     int *d_sched;
@@ -260,9 +263,20 @@ static int plan_geometry(weaklabel_plan *pl) {
             }
         }
     }
-    if (pl->tune_path == 2 && pl->fG == 0)
+    pl->v2_ok = v2_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, pl->tune_nt, &pl->v2);
+    if (pl->v2_ok) {
+        int vs = pl->tune_slots ? pl->tune_slots : pl->v2.max_clusters;
+        if (vs > pl->v2.max_clusters) vs = pl->v2.max_clusters;
+        if (vs > pl->B) vs = pl->B;
+        if (vs < 1) vs = 1;
+        pl->v2_slots = vs;
+    }
+    if (pl->tune_path == 2 && !pl->v2_ok)
         return fail(WEAKLABEL_ERR_ARG, "the fast path cannot hold %d pixels with this cluster/tile tuning", N);
-    const int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
+    if (pl->tune_path == 3 && pl->fG == 0)
+        return fail(WEAKLABEL_ERR_ARG, "the first-generation fast path cannot hold %d pixels with this cluster/tile tuning", N);
+    int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
+    if (pl->v2_ok && pl->v2_slots > ss) ss = pl->v2_slots;
     pl->scratch_slots = ss;
     CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 1) * pl->Npad * sizeof(float)));
     CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)ss * pl->Npad));
@@ -300,6 +314,8 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean1, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_shift, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_sched, (size_t)B * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_prof, (size_t)B * 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(pl->d_prof, 0, (size_t)B * 8 * sizeof(unsigned long long));
     if (e != cudaSuccess) {
         weaklabel_plan_destroy(pl);
         return fail(WEAKLABEL_ERR_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
@@ -313,7 +329,7 @@ extern "C" WL_API void weaklabel_plan_destroy(weaklabel_plan *pl) {
     cudaSetDevice(pl->device);
     plan_free_geometry(pl);
     cudaFree(pl->d_counter); cudaFree(pl->d_meta); cudaFree(pl->d_order); cudaFree(pl->d_bias);
-    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift); cudaFree(pl->d_sched);
+    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift); cudaFree(pl->d_sched); cudaFree(pl->d_prof);
     delete pl;
 }
 
@@ -331,11 +347,30 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
 extern "C" WL_API long long weaklabel_plan_launches(const weaklabel_plan *pl) { return pl ? pl->launches : 0; }
 
 extern "C" WL_API int weaklabel_plan_set_path(weaklabel_plan *pl, int path) {
-    if (!pl || path < 0 || path > 2) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic) or 2 (fast)");
+    if (!pl || path < 0 || path > 3) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2 (fast) or 3 (first-generation fast)");
     pl->tune_path = path;
     return WEAKLABEL_OK;
 }
 extern "C" WL_API int weaklabel_plan_last_path(const weaklabel_plan *pl) { return pl ? pl->last_path : 0; }
+
+extern "C" WL_API int weaklabel_plan_set_threads(weaklabel_plan *pl, int threads_per_cta) {
+    if (!pl || (threads_per_cta != 0 && threads_per_cta != 512 && threads_per_cta != 1024))
+        return fail(WEAKLABEL_ERR_ARG, "threads per CTA must be 0 (auto), 512 or 1024");
+    CUDA_TRY(cudaSetDevice(pl->device));
+    if (pl->last_stream || pl->geometry_ok) CUDA_TRY(cudaDeviceSynchronize());
+    plan_free_geometry(pl);
+    pl->tune_nt = threads_per_cta;
+    return WEAKLABEL_OK;
+}
+
+extern "C" WL_API int weaklabel_plan_profile(weaklabel_plan *pl, int enable, unsigned long long *out) {
+    if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
+    CUDA_TRY(cudaSetDevice(pl->device));
+    if (pl->last_stream) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
+    if (out) CUDA_TRY(cudaMemcpy(out, pl->d_prof, (size_t)pl->B * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    pl->prof_on = enable != 0;
+    return WEAKLABEL_OK;
+}
 
 extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned char *present,
                                       bool suppress_others, int num_iter, float margin_others,
@@ -436,14 +471,21 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.planes = pl->d_planes; p.absent_idx = pl->d_absidx; p.ctl = pl->d_ctl;
     // the on-chip fast path covers suppress_others with a margin >= 0 on contiguous pixels
     // (weaklabel.cpp:45-65 then guarantees that no absent class exceeds a present one)
-    const bool fast_ok = pl->fG > 0 && pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
-    if (pl->tune_path == 2 && !fast_ok)
+    const bool cond_ok = pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
+    const bool v2_ok = pl->v2_ok && cond_ok;
+    const bool fast1_ok = pl->fG > 0 && cond_ok;
+    if (pl->tune_path == 2 && !v2_ok)
         return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
                     "contiguous pixels)");
-    const bool fast = fast_ok && pl->tune_path != 1;
+    if (pl->tune_path == 3 && !fast1_ok)
+        return fail(WEAKLABEL_ERR_ARG, "first-generation fast path forced but not applicable");
+    const int path = pl->tune_path ? pl->tune_path : (v2_ok ? 2 : 1);
     int slots_used = pl->slots;
     p.Npad = pl->Npad; p.sub_px = pl->sub_px;
-    if (fast) {
+    if (path == 2) {
+        p.TS = pl->v2.TS; p.ntiles = pl->v2.G; p.L = pl->v2.L; p.G = pl->v2.G; p.sub_px = pl->v2.cpx;
+        slots_used = pl->v2_slots;
+    } else if (path == 3) {
         p.TS = pl->fTS; p.ntiles = (pl->N + pl->fTS - 1) / pl->fTS; p.L = pl->fL; p.G = pl->fG;
         slots_used = pl->fslots;
     } else {
@@ -453,11 +495,13 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.image_counter = pl->d_counter; p.status = pl->d_counter + 1;
     p.labels = d_labels; p.bias_out = pl->d_bias;
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
+    p.prof = pl->prof_on ? pl->d_prof : nullptr;
     CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
-    CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
-    if (fast) CUDA_TRY(launch_estep_fast(p, slots_used, st));
+    if (path != 2) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
+    if (path == 2) CUDA_TRY(launch_estep_v2(p, pl->v2, slots_used, st));
+    else if (path == 3) CUDA_TRY(launch_estep_fast(p, slots_used, st));
     else CUDA_TRY(launch_estep(p, slots_used, st));
-    pl->last_path = fast ? 2 : 1;
+    pl->last_path = path;
     pl->launches += 1;
     pl->last_stream = st;
     return WEAKLABEL_OK;

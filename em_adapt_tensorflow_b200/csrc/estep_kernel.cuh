@@ -57,6 +57,7 @@ struct EStepParams {
     float *mean0;             // [B]
     double *mean1;            // [B]
     double *shift;            // [B]  (double)mean0 - mean1
+    unsigned long long *prof; // [B][8] phase time stamps (globaltimer ns) or NULL
 };
 
 size_t estep_smem_bytes();
@@ -69,6 +70,13 @@ constexpr int FAST_PPT_MAX = 33;
 int fast_ppt_for(int tile_pixels);                     // 0 when the tile does not fit
 cudaError_t launch_estep_fast(const EStepParams &p, int n_clusters, cudaStream_t stream);
 int estep_fast_max_clusters(int G, int tile_pixels);
+
+// second-generation kernel of the common configuration (estep_v2.cu)
+constexpr int V2_PPT_SMALL = 4;
+constexpr int V2_PPT_MAX = 33;
+struct V2Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
+bool v2_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, int tune_nt, V2Config *out);
+cudaError_t launch_estep_v2(const EStepParams &p, const V2Config &cfg, int n_clusters, cudaStream_t stream);
 
 struct FinalizeParams {
     float *map; long long s0, s2;

@@ -147,9 +147,18 @@ WL_API int weaklabel_plan_tune(weaklabel_plan *plan, int cluster_size, int tile_
 /* Two kernels implement the E-step: the on-chip fast path (suppress_others with a margin
  * >= 0, contiguous pixels, image fits the cluster) and the generic one (everything else).
  * path: 0 = choose automatically (default), 1 = force generic, 2 = force fast (run() fails if
- * it does not apply).  weaklabel_plan_last_path: which one the last run() launched. */
+ * it does not apply), 3 = the first-generation fast kernel (kept for A/B measurements).
+ * weaklabel_plan_last_path: which one the last run() launched. */
 WL_API int weaklabel_plan_set_path(weaklabel_plan *plan, int path);
 WL_API int weaklabel_plan_last_path(const weaklabel_plan *plan);
+/* threads per CTA of the fast kernel: 0 = auto, 1024 (one CTA per SM) or 512 (two CTAs per SM,
+ * clusters twice as large). */
+WL_API int weaklabel_plan_set_threads(weaklabel_plan *plan, int threads_per_cta);
+/* Per-image phase time stamps of the fast kernel (globaltimer ns): out[B][8] = {claimed,
+ * streamed-in, mean_max_0 done, iterations done, mean_max_1 done, labels written, selections
+ * performed, label-set size}.  Reads the stamps of the last run into `out` (may be NULL), then
+ * enables (1) / disables (0) stamping for the following runs. */
+WL_API int weaklabel_plan_profile(weaklabel_plan *plan, int enable, unsigned long long *out);
 /* kernels launched by this plan since creation (bench.py's gpu_launches) */
 WL_API long long weaklabel_plan_launches(const weaklabel_plan *plan);
 

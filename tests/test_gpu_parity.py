@@ -32,7 +32,7 @@ def _fast_applies(p):
     return bool(p["suppress_others"]) and p["margin_others"] >= 0
 
 
-def _device_run(f, l, p, tune=None, want_map=True, path="auto"):
+def _device_run(f, l, p, tune=None, want_map=True, path="auto", threads=0):
     torch = _torch()
     B, H, W, C = f.shape
     t = torch.from_numpy(np.ascontiguousarray(f)).cuda()
@@ -40,6 +40,8 @@ def _device_run(f, l, p, tune=None, want_map=True, path="auto"):
     if tune:
         plan.tune(*tune)
     plan.set_path(path)
+    if threads:
+        plan.set_threads(threads)
     plan.prepare(wl.label_set(l, C), p["suppress_others"], p["num_iter"], p["margin_others"], p["bg"], p["fg"],
                  rng=wl.OrderStream(1))
     lab = plan.labels(t)
@@ -133,10 +135,11 @@ def test_forced_geometries(name, tune):
 FAST_TUNES = [(1, 0, 0), (2, 0, 0), (4, 0, 0), (8, 0, 1), (16, 0, 0), (2, 1200, 0), (1, 4100, 0), (2, 5000, 2)]
 
 
+@pytest.mark.parametrize("variant", ["fast", "fast-512", "fast1"])
 @pytest.mark.parametrize("tune", FAST_TUNES)
 @pytest.mark.parametrize("name", ["c1_41_p2", "p5_seq3", "p21_41", "allneg_p3", "ties_int", "ties_const", "shape_7x5",
                                   "shape_1x1", "mag_big", "mag_tiny", "rank_last", "c2_41_b30", "shape_100x37"])
-def test_fast_path_forced_geometries(name, tune):
+def test_fast_path_forced_geometries(name, tune, variant):
     """On-chip fast kernel: cluster sizes 1..16 (DSMEM exchange), tiles larger than the image
     (idle CTAs), both per-thread pixel counts (tile > 4096 pixels selects the 33-pixel build)."""
     f, l, p = cases.build_case(name)
@@ -145,7 +148,8 @@ def test_fast_path_forced_geometries(name, tune):
     if TS and G * TS < N:
         pytest.skip("tile tuning does not hold the image")
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
-    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="fast")
+    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(
+        f, l, p, tune=tune, path=variant.split("-")[0], threads=512 if variant.endswith("512") else 0)
     assert bias_g.tobytes() == bias_o.tobytes()
     assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
     assert np.array_equal(got_lab, want_lab)
