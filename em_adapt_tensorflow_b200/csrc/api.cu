@@ -158,6 +158,41 @@ extern "C" WL_API int weaklabel_draw_order_host(const unsigned char *present, in
 }
 
 // ---------------------------------------------------------------------------------------------
+// debugging aid (WEAKLABEL_V3_TRAIL=1): progress words of every CTA of the warp-specialised kernel
+// in mapped host memory, printed at process exit -- they survive a device-side exception
+// ---------------------------------------------------------------------------------------------
+static unsigned int *g_trail = nullptr;
+static void trail_dump() {
+    if (!g_trail) return;
+    for (int cta = 0; cta < 160; cta++) {
+        const unsigned int *w = g_trail + cta * 16;
+        bool any = false;
+        for (int k = 0; k < 16; k++) any = any || w[k];
+        if (!any) continue;
+        fprintf(stderr, "trail cta %3d:", cta);
+        for (int k = 0; k < 16; k++) fprintf(stderr, " %08x", w[k]);
+        fprintf(stderr, "\n");
+    }
+}
+static volatile unsigned int *debug_trail() {
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        if (getenv("WEAKLABEL_V3_TRAIL")) {
+            void *h = nullptr;
+            if (cudaHostAlloc(&h, 160 * 16 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+                memset(h, 0, 160 * 16 * sizeof(unsigned int));
+                g_trail = (unsigned int *)h;
+                atexit(trail_dump);
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
+    return g_trail;
+}
+
+// ---------------------------------------------------------------------------------------------
 // plans
 // ---------------------------------------------------------------------------------------------
 struct weaklabel_plan {
@@ -167,6 +202,7 @@ struct weaklabel_plan {
     int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 fast (v2), 3 first-generation fast
     int tune_nt;                                    // v2 threads per CTA (0 auto, 512, 1024)
     V2Config v2; bool v2_ok; int v2_slots;          // second-generation kernel (estep_v2.cu)
+    V3Config v3; bool v3_ok; int v3_slots;          // third-generation kernel (estep_v3.cu), tune_path 4
     unsigned long long *d_prof; bool prof_on;       // [B][8] phase time stamps
     bool geometry_ok;
     int scratch_slots;
@@ -271,14 +307,25 @@ static int plan_geometry(weaklabel_plan *pl) {
         if (vs < 1) vs = 1;
         pl->v2_slots = vs;
     }
+    pl->v3_ok = (pl->tune_nt == 0) && v3_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, &pl->v3);
+    if (pl->v3_ok) {
+        int vs = pl->tune_slots ? pl->tune_slots : pl->v3.max_clusters;
+        if (vs > pl->v3.max_clusters) vs = pl->v3.max_clusters;
+        if (vs > pl->B) vs = pl->B;
+        if (vs < 1) vs = 1;
+        pl->v3_slots = vs;
+    }
     if (pl->tune_path == 2 && !pl->v2_ok)
         return fail(WEAKLABEL_ERR_ARG, "the fast path cannot hold %d pixels with this cluster/tile tuning", N);
+    if (pl->tune_path == 4 && !pl->v3_ok)
+        return fail(WEAKLABEL_ERR_ARG, "the warp-specialised fast path cannot hold %d pixels with this cluster/tile tuning", N);
     if (pl->tune_path == 3 && pl->fG == 0)
         return fail(WEAKLABEL_ERR_ARG, "the first-generation fast path cannot hold %d pixels with this cluster/tile tuning", N);
     int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
     if (pl->v2_ok && pl->v2_slots > ss) ss = pl->v2_slots;
+    if (pl->v3_ok && 2 * pl->v3_slots > ss) ss = 2 * pl->v3_slots;      // two plane sets per resident cluster
     pl->scratch_slots = ss;
-    CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 1) * pl->Npad * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 2) * pl->Npad * sizeof(float)));
     CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)ss * pl->Npad));
     CUDA_TRY(cudaMalloc(&pl->d_ctl, (size_t)ss * sizeof(SlotCtl)));
     pl->geometry_ok = true;
@@ -347,7 +394,7 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
 extern "C" WL_API long long weaklabel_plan_launches(const weaklabel_plan *pl) { return pl ? pl->launches : 0; }
 
 extern "C" WL_API int weaklabel_plan_set_path(weaklabel_plan *pl, int path) {
-    if (!pl || path < 0 || path > 3) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2 (fast) or 3 (first-generation fast)");
+    if (!pl || path < 0 || path > 4) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2 (second-generation fast), 3 (first-generation fast) or 4 (warp-specialised fast)");
     pl->tune_path = path;
     return WEAKLABEL_OK;
 }
@@ -474,17 +521,27 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     const bool cond_ok = pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
     const bool v2_ok = pl->v2_ok && cond_ok;
     const bool fast1_ok = pl->fG > 0 && cond_ok;
+    const bool v3_ok = pl->v3_ok && cond_ok;
+    if (pl->tune_path == 4 && !v3_ok)
+        return fail(WEAKLABEL_ERR_ARG, "warp-specialised fast path forced but not applicable (needs suppress_others, "
+                    "margin >= 0, contiguous pixels)");
     if (pl->tune_path == 2 && !v2_ok)
         return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
                     "contiguous pixels)");
     if (pl->tune_path == 3 && !fast1_ok)
         return fail(WEAKLABEL_ERR_ARG, "first-generation fast path forced but not applicable");
-    const int path = pl->tune_path ? pl->tune_path : (v2_ok ? 2 : 1);
+    const int path = pl->tune_path ? pl->tune_path : (v3_ok ? 4 : (v2_ok ? 2 : 1));
     int slots_used = pl->slots;
     p.Npad = pl->Npad; p.sub_px = pl->sub_px;
     if (path == 2) {
         p.TS = pl->v2.TS; p.ntiles = pl->v2.G; p.L = pl->v2.L; p.G = pl->v2.G; p.sub_px = pl->v2.cpx;
         slots_used = pl->v2_slots;
+    } else if (path == 4) {
+        p.TS = pl->v3.TS; p.ntiles = pl->v3.G; p.L = pl->v3.L; p.G = pl->v3.G; p.sub_px = pl->v3.cpx;
+        slots_used = pl->v3_slots;
+        const char *pf = getenv("WEAKLABEL_V3_PREFETCH");          // tuning knob: chunks of L2 prefetch distance
+        p.pf_ahead = pf ? atoi(pf) : V3_PF_AHEAD;
+        p.trail = debug_trail();
     } else if (path == 3) {
         p.TS = pl->fTS; p.ntiles = (pl->N + pl->fTS - 1) / pl->fTS; p.L = pl->fL; p.G = pl->fG;
         slots_used = pl->fslots;
@@ -497,8 +554,9 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
     p.prof = pl->prof_on ? pl->d_prof : nullptr;
     CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
-    if (path != 2) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
-    if (path == 2) CUDA_TRY(launch_estep_v2(p, pl->v2, slots_used, st));
+    if (path != 2 && path != 4) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
+    if (path == 4) CUDA_TRY(launch_estep_v3(p, pl->v3, slots_used, st));
+    else if (path == 2) CUDA_TRY(launch_estep_v2(p, pl->v2, slots_used, st));
     else if (path == 3) CUDA_TRY(launch_estep_fast(p, slots_used, st));
     else CUDA_TRY(launch_estep(p, slots_used, st));
     pl->last_path = path;

@@ -48,6 +48,7 @@ struct EStepParams {
     SlotCtl *ctl;             // [slots]
     int Npad, TS, ntiles, L, G;
     int sub_px;               // pixels per streaming sub-tile
+    int pf_ahead;             // v3: chunks prefetched into the L2 ahead of the staging ring
     int *image_counter;
     const int *sched;         // [B] order in which images are claimed (largest label sets first), or NULL
     int *status;              // device-side error flag (0 = ok)
@@ -58,6 +59,7 @@ struct EStepParams {
     double *mean1;            // [B]
     double *shift;            // [B]  (double)mean0 - mean1
     unsigned long long *prof; // [B][8] phase time stamps (globaltimer ns) or NULL
+    volatile unsigned int *trail;  // v3 debugging: [CTA][16] progress words in mapped host memory, or NULL
 };
 
 size_t estep_smem_bytes();
@@ -77,6 +79,23 @@ constexpr int V2_PPT_MAX = 33;
 struct V2Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
 bool v2_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, int tune_nt, V2Config *out);
 cudaError_t launch_estep_v2(const EStepParams &p, const V2Config &cfg, int n_clusters, cudaStream_t stream);
+
+// third-generation kernel (estep_v3.cu): warp-specialised, producers stream image t+1 while the
+// compute threads work on image t; the scratch holds TWO plane sets per resident cluster
+constexpr int V3_NT = 896;            // compute threads per CTA
+constexpr int V3_NPW = 4;             // producer warps per CTA
+constexpr int V3_NST = 8;             // stages of the staging ring: a multiple of V3_NPW, so that a stage is
+                                      // always filled for, and drained by, the same warp (which then waits for
+                                      // its phases in order -- a warp must never wait one phase ahead)
+constexpr int V3_STAGE_BYTES = 7168;
+constexpr int V3_PF_AHEAD = 16;       // chunks prefetched into the L2 ahead of the ring
+constexpr int V3_MAXG = 8;
+constexpr int V3_PPT_SMALL = 4;
+constexpr int V3_PPT_MID = 12;
+constexpr int V3_PPT_MAX = 37;
+struct V3Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
+bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out);
+cudaError_t launch_estep_v3(const EStepParams &p, const V3Config &cfg, int n_clusters, cudaStream_t stream);
 
 struct FinalizeParams {
     float *map; long long s0, s2;
