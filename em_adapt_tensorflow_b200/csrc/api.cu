@@ -165,12 +165,12 @@ static unsigned int *g_trail = nullptr;
 static void trail_dump() {
     if (!g_trail) return;
     for (int cta = 0; cta < 160; cta++) {
-        const unsigned int *w = g_trail + cta * 16;
+        const unsigned int *w = g_trail + cta * 32;
         bool any = false;
-        for (int k = 0; k < 16; k++) any = any || w[k];
+        for (int k = 0; k < 32; k++) any = any || w[k];
         if (!any) continue;
         fprintf(stderr, "trail cta %3d:", cta);
-        for (int k = 0; k < 16; k++) fprintf(stderr, " %08x", w[k]);
+        for (int k = 0; k < 32; k++) fprintf(stderr, " %08x", w[k]);
         fprintf(stderr, "\n");
     }
 }
@@ -180,8 +180,8 @@ static volatile unsigned int *debug_trail() {
         tried = true;
         if (getenv("WEAKLABEL_V3_TRAIL")) {
             void *h = nullptr;
-            if (cudaHostAlloc(&h, 160 * 16 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
-                memset(h, 0, 160 * 16 * sizeof(unsigned int));
+            if (cudaHostAlloc(&h, 160 * 32 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+                memset(h, 0, 160 * 32 * sizeof(unsigned int));
                 g_trail = (unsigned int *)h;
                 atexit(trail_dump);
             } else {

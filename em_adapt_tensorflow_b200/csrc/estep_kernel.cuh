@@ -89,9 +89,10 @@ constexpr int V3_NST = 8;             // stages of the staging ring: a multiple 
                                       // its phases in order -- a warp must never wait one phase ahead)
 constexpr int V3_STAGE_BYTES = 7168;
 constexpr int V3_PF_AHEAD = 16;       // chunks prefetched into the L2 ahead of the ring
-constexpr int V3_MAXG = 8;
+constexpr int V3_MAXG = 9;
 constexpr int V3_PPT_SMALL = 4;
 constexpr int V3_PPT_MID = 12;
+constexpr int V3_PPT_BIG = 33;
 constexpr int V3_PPT_MAX = 37;
 struct V3Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
 bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out);

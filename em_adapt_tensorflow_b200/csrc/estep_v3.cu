@@ -32,7 +32,7 @@ constexpr int NB2 = 2048;               // fine bins per histogram round
 constexpr int NB1 = 64;                 // super bins (32 fine bins each) exchanged through DSMEM
 constexpr int SUBB = NB2 / NB1;
 constexpr int GCAP = 1024;              // candidates gathered into every CTA
-constexpr int MBW = 80;                 // mailbox words per CTA per exchange
+constexpr int MBW = 72;                 // mailbox words per CTA per exchange
 constexpr int WIN_UNDER = 33;           // bin 0: zero margins; 1..32: below the window, by exponent group
 constexpr int WIN_BINADES = 31;
 constexpr int WIN_SH = 17;              // 64 bins per binade inside the window
@@ -126,6 +126,7 @@ struct Misc {
     float hbias[MAXC][HCAP];            // bias history per plane (weaklabel.cpp:90-92)
     int hn[MAXC];
     uint64_t full_bar[NST];             // producers: stage filled (bulk-copy bytes landed)
+    uint64_t e0_bar;                    // compute: E0 of my tile landed in shared memory
     uint32_t pstat[2][NPW][8];          // producers -> compute: zero counts [0..3], largest margin [4] per warp
     uint64_t cmd_bar[2];                // compute -> producers: image of sequence parity q may be streamed
     uint64_t ready_bar[2];              // producers -> compute: planes of sequence parity q are in the scratch
@@ -195,7 +196,7 @@ template <int NT_> struct Cx {
 };
 
 template <int NT_> __device__ __forceinline__ void trc(const Cx<NT_> &c, int k, uint32_t v) {
-    if (c.p->trail && c.tid == 0) c.p->trail[blockIdx.x * 16 + k] = v;
+    if (c.p->trail && c.tid == 0) c.p->trail[blockIdx.x * 32 + k] = v;
 }
 
 // Cluster-wide barrier of the COMPUTE threads (the producers never take part): every CTA arrives
@@ -431,7 +432,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         const uint32_t n = w.nbase + (uint32_t)q;
         const int d = (int)(n % NST);
         mbar_wait(&w.ms->full_bar[d], (n / NST) & 1u);
-        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 16 + 8 + w.pw] = ((uint32_t)par << 28) | ((uint32_t)(b & 0xfff) << 16) | (uint32_t)q;
+        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 32 + 8 + w.pw] = ((uint32_t)par << 28) | ((uint32_t)(b & 0xfff) << 16) | (uint32_t)q;
         const float *stage = reinterpret_cast<const float *>(w.staging + (size_t)d * STAGE_BYTES);
         const int npx = min(cpx, w.n_t - q * cpx);
         const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
@@ -550,7 +551,7 @@ __device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, un
     w.nbase = 0;
     for (uint32_t s = 0;; s++) {
         const int q = s & 1u;
-        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 16 + 12 + w.pw] = (s << 8) | 1u;
+        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 32 + 12 + w.pw] = (s << 8) | 1u;
         mbar_wait(&ms->cmd_bar[q], (s >> 1) & 1u);
         const int b = *reinterpret_cast<volatile int *>(&ms->cmd_img[q]);
         if (b >= p.B) break;
@@ -561,7 +562,7 @@ __device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, un
         __threadfence();                                        // my plane/E0 stores have reached the L2 (the
         __syncwarp();                                           // E0 tile is fetched from there by the copy engine)
         if (w.lane == 0) mbar_arrive(&ms->ready_bar[q]);        // release: planes and statistics of my chunks
-        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 16 + 12 + w.pw] = (s << 8) | 2u;
+        if (p.trail && w.lane == 0) p.trail[blockIdx.x * 32 + 12 + w.pw] = (s << 8) | 2u;
     }
 }
 
@@ -843,13 +844,16 @@ __device__ __forceinline__ void hist_pass(Cx<NT_> &c, const float (&x)[PPT], uin
         const bool valid = i < c.n_t;
         const uint32_t key = valid ? __float_as_uint(__fsub_rn(c.s_E[i], x[j])) : 0xffffffffu;
         if (WINDOW) {
-            zeros += __popc(__ballot_sync(0xffffffffu, key == 0u));
+            zeros += (key == 0u) ? 1u : 0u;
             if (valid && key != 0u) atomicAdd(&h[win_bin(key, lo)], 1u);
         } else {
             if (valid && key >= lo && key <= hi) atomicAdd(&h[(key - lo) >> sh], 1u);
         }
     }
-    if (WINDOW && c.lane == 0 && zeros) atomicAdd(&h[0], zeros);
+    if (WINDOW) {
+        zeros = __reduce_add_sync(0xffffffffu, zeros);
+        if (c.lane == 0 && zeros) atomicAdd(&h[0], zeros);
+    }
     csync<NT_>();
 }
 
@@ -971,11 +975,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, const float (&x)[PPT]
         uint32_t *h = ss->hist[c.hround & 1u];
         if (window) hist_pass<NT_, PPT, true>(c, x, lo, hi, sh, h);
         else hist_pass<NT_, PPT, false>(c, x, lo, hi, sh, h);
-        trc(c, 3, 0x10u + (uint32_t)guard);
         const Located L = locate(c, r);
-        trc(c, 3, 0x20u + (uint32_t)guard);
-        trc(c, 4, (uint32_t)L.bin);
-        trc(c, 5, L.cnt);
         if (L.bin < 0) {
             if (c.tid == 0) atomicExch(c.p->status, 200 + guard);
             return 0.f;
@@ -1017,11 +1017,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, const float (&x)[PPT]
             } else {
                 for (uint32_t w = c.tid; w < mine; w += NT_) ss->gather[w] = ss->mylist[w];
             }
-            trc(c, 3, 0x30u);
-            trc(c, 6, mine);
-            trc(c, 7, off);
             cluster_sync_compute(c);
-            trc(c, 3, 0x40u);
             return __uint_as_float(local_select(c, ss->gather, L.cnt, r, klo, khi));
         }
         // heavy ties or a coarse (out-of-window) bin: narrow the bracket and bin again
@@ -1078,12 +1074,17 @@ __device__ __forceinline__ void write_labels(Cx<NT_> &c, double shift) {
         int bi[4] = {0, 0, 0, 0};
         for (int pl = 0; pl < c.P; pl++) {
             const float4 v = __ldcg(reinterpret_cast<const float4 *>(c.planes + (size_t)pl * p.Npad + idx));
-            const Hist h = load_hist(c.ms, pl);
-            const float vv[4] = {v.x, v.y, v.z, v.w};
+            float vv[4] = {v.x, v.y, v.z, v.w};
+            const int hn = c.ms->hn[pl];
+            for (int k = 0; k < hn; k++) {
+                const float hb = c.ms->hbias[pl][k];
+#pragma unroll
+                for (int e = 0; e < 4; e++) vv[e] = __fadd_rn(vv[e], hb);
+            }
             const int cls = c.ms->plist[pl];
 #pragma unroll
             for (int e = 0; e < 4; e++) {
-                const float fv = __double2float_rn(__dadd_rn((double)with_hist(vv[e], h), shift));
+                const float fv = __double2float_rn(__dadd_rn((double)vv[e], shift));
                 if (fv > best[e]) { best[e] = fv; bi[e] = cls; }
                 if (fv < lowest[e]) lowest[e] = fv;
             }
@@ -1153,6 +1154,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
     c.n_t = max(0, min(p.TS, p.N - c.base));
     if (c.tid == 0) {
         for (int d = 0; d < NST; d++) mbar_init(&c.ms->full_bar[d], 1);
+        mbar_init(&c.ms->e0_bar, 1);
         for (int q = 0; q < 2; q++) {
             mbar_init(&c.ms->cmd_bar[q], 1);
             mbar_init(&c.ms->ready_bar[q], NPW);
@@ -1216,27 +1218,19 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
         mbar_wait(&c.ms->ready_bar[seq & 1u], (seq >> 1) & 1u);
         trc(c, 0, (seq << 8) | 3u);
         trc(c, 1, (uint32_t)c.b);
-        {
-            // (a bulk copy of the tile into shared memory was tried here and dropped: with every
-            // cluster of the device active it intermittently ended in a launch failure)
-            const float *src = c.planes + (size_t)(p.C + 1) * p.Npad + c.base;
-            constexpr int JB = 8;
-#pragma unroll 1
-            for (int j0 = 0; j0 < PPT; j0 += JB) {
-                float v[JB];
-#pragma unroll
-                for (int e = 0; e < JB; e++) {
-                    const int i = (j0 + e) * NT_ + c.tid;
-                    v[e] = (j0 + e < PPT && i < c.n_t) ? __ldcg(src + i) : 0.f;
-                }
-#pragma unroll
-                for (int e = 0; e < JB; e++) {
-                    const int i = (j0 + e) * NT_ + c.tid;
-                    if (j0 + e < PPT && i < c.n_t) c.s_E[i] = v[e];
-                }
+        if (c.tid == 0) {
+            const uint32_t bytes = (uint32_t)((c.n_t + 3) & ~3) * 4u;
+            if (bytes) {
+                asm volatile("fence.proxy.async;\n" ::: "memory");   // generic accesses to s_E (previous image) first
+                mbar_expect_tx(&c.ms->e0_bar, bytes);
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
+                for (uint32_t o = 0; o < bytes; o += 32768u)
+                    bulk_g2s(reinterpret_cast<unsigned char *>(c.s_E) + o, src + o, min(32768u, bytes - o), &c.ms->e0_bar);
+            } else {
+                mbar_arrive(&c.ms->e0_bar);
             }
         }
-        csync<NT_>();
+        mbar_wait(&c.ms->e0_bar, seq & 1u);
         if (prof && lead_thread) prof[1] = gtimer();
 
         trc(c, 0, (seq << 8) | 4u);
@@ -1298,11 +1292,16 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
                     trc(c, 2, ((uint32_t)j << 8) | (uint32_t)t);
                     float x[PPT];
                     float *plc = c.planes + (size_t)plane * p.Npad + c.base;
-                    const Hist h = load_hist(c.ms, plane);
+                    const int hn = c.ms->hn[plane];
 #pragma unroll
                     for (int q = 0; q < PPT; q++) {
                         const int i = q * NT_ + c.tid;
-                        x[q] = (i < c.n_t) ? with_hist(__ldcg(plc + i), h) : 0.f;
+                        x[q] = (i < c.n_t) ? __ldcg(plc + i) : 0.f;
+                    }
+                    for (int e = 0; e < hn; e++) {          // the biases the class received so far, in order
+                        const float hb = c.ms->hbias[plane][e];
+#pragma unroll
+                        for (int q = 0; q < PPT; q++) x[q] = __fadd_rn(x[q], hb);
                     }
                     uint32_t e_top = (__float_as_uint(dmax_bound) >> 23) + 1u;
                     if (e_top > 254u) e_top = 254u;
@@ -1312,7 +1311,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
                     csync<NT_>();
                     if (bias != 0.f) {
                         // fold: x += bias (weaklabel.cpp:90-92), E = max(E, x) (:94-99)
-                        const bool rewrite = (h.n == HCAP);
+                        const bool rewrite = (hn == HCAP);
                         uint32_t gained = 0u, znew = 0u;
 #pragma unroll
                         for (int q = 0; q < PPT; q++) {
@@ -1335,7 +1334,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
                         }
                         if (c.tid == 0) {
                             if (rewrite) { c.ms->hn[plane] = 0; }
-                            else { c.ms->hbias[plane][h.n] = bias; c.ms->hn[plane] = h.n + 1; }
+                            else { c.ms->hbias[plane][hn] = bias; c.ms->hn[plane] = hn + 1; }
                         }
                         dmax_bound = __fadd_rn(dmax_bound, bias);
                     } else if (zeros != 0xffffffffu) {
@@ -1392,6 +1391,8 @@ static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t s
     const size_t smem = Layout<NT_>::total(PPT);
     cudaError_t e = cudaFuncSetAttribute(estep_v3_kernel<NT_, PPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(estep_v3_kernel<NT_, PPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((max_clusters ? 64 : n_clusters) * p.G));
     cfg.blockDim = dim3(NT_ + NPW * 32);
@@ -1415,6 +1416,7 @@ static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t s
 
 static cudaError_t dispatch(const EStepParams &p, int ppt, int n_clusters, cudaStream_t stream, int *maxc) {
     if (ppt == V3_PPT_MAX) return launch_t<V3_NT, V3_PPT_MAX>(p, n_clusters, stream, maxc);
+    if (ppt == V3_PPT_BIG) return launch_t<V3_NT, V3_PPT_BIG>(p, n_clusters, stream, maxc);
     if (ppt == V3_PPT_MID) return launch_t<V3_NT, V3_PPT_MID>(p, n_clusters, stream, maxc);
     if (ppt == V3_PPT_SMALL) return launch_t<V3_NT, V3_PPT_SMALL>(p, n_clusters, stream, maxc);
     return cudaErrorInvalidValue;
@@ -1422,24 +1424,18 @@ static cudaError_t dispatch(const EStepParams &p, int ppt, int n_clusters, cudaS
 
 }  // namespace v3
 
-// Geometry of the v3 kernel for an image of N pixels with C classes.  tune_G = 0: automatic.
-bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out) {
+// Geometry of the v3 kernel for an image of N pixels with C classes and a given cluster size.
+static bool v3_try(int N, int C, int G, int tune_TS, V3Config *out) {
     const int nt = V3_NT;
     const int cap = V3_PPT_MAX * nt;
-    int G = tune_G;
-    if (G == 0) {
-        G = 1;
-        while (G < V3_MAXG && (N + G - 1) / G > cap) G *= 2;
-        while (G < 8 && (long long)B * G * 2 <= sms && N / (2 * G) >= 4096) G *= 2;
-    }
-    if (G != 1 && G != 2 && G != 4 && G != 8) return false;
+    if (G < 1 || G > V3_MAXG) return false;
     int TS = tune_TS ? tune_TS : (N + G - 1) / G;
     TS = (TS + 3) / 4 * 4;
     if (TS < 4) TS = 4;
     if (TS > cap || (long long)TS * G < N) return false;
     const int need = (TS + nt - 1) / nt;
     out->nt = nt;
-    out->ppt = need <= V3_PPT_SMALL ? V3_PPT_SMALL : (need <= V3_PPT_MID ? V3_PPT_MID : V3_PPT_MAX);
+    out->ppt = need <= V3_PPT_SMALL ? V3_PPT_SMALL : (need <= V3_PPT_MID ? V3_PPT_MID : (need <= V3_PPT_BIG ? V3_PPT_BIG : V3_PPT_MAX));
     out->G = G;
     out->TS = TS;
     out->L = need | 1;                                   // odd: conflict-free chunk walks
@@ -1454,6 +1450,23 @@ bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Confi
         return false;
     }
     out->max_clusters = maxc;
+    return true;
+}
+
+// tune_G = 0: automatic -- the smallest power-of-two cluster that holds the image; large batches of
+// large images also try clusters of 9 (non-portable size): on B200 as many of them are co-resident
+// as clusters of 8 (15), so 135 instead of 120 SMs work and every thread holds fewer pixels.
+bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out) {
+    if (tune_G) return v3_try(N, C, tune_G, tune_TS, out);
+    const int cap = V3_PPT_MAX * V3_NT;
+    int G = 1;
+    while (G < 8 && (N + G - 1) / G > cap) G *= 2;
+    while (G < 8 && (long long)B * G * 2 <= sms && N / (2 * G) >= 4096) G *= 2;
+    if (!v3_try(N, C, G, tune_TS, out)) return false;
+    if (G == 8 && tune_TS == 0) {
+        V3Config alt;
+        if (v3_try(N, C, 9, 0, &alt) && alt.max_clusters >= out->max_clusters && B >= alt.max_clusters) *out = alt;
+    }
     return true;
 }
 
