@@ -758,9 +758,15 @@ __device__ __forceinline__ T exact_sum(Cx<NT_> &c, double cpre, double cs, doubl
                 int hk = NT_, tk = NT_ - 1;
                 ChunkFn<T> pk = chunk_identity<T>();
                 if (kk < nh) {
-                    hk = (int)ld_peer16(peer_addr(&ss->heads[kk], r));
-                    if (kk + 1 < nh) tk = (int)ld_peer16(peer_addr(&ss->heads[kk + 1], r)) - 1;
-                    pk = IO::ld_peer_fn(&ss->pf[tk], r);
+                    if (r == 0) {                           // my own tile
+                        hk = (int)ss->heads[kk];
+                        if (kk + 1 < nh) tk = (int)ss->heads[kk + 1] - 1;
+                        pk = ss->pf[tk];
+                    } else {
+                        hk = (int)ld_peer16(peer_addr(&ss->heads[kk], r));
+                        if (kk + 1 < nh) tk = (int)ld_peer16(peer_addr(&ss->heads[kk + 1], r)) - 1;
+                        pk = IO::ld_peer_fn(&ss->pf[tk], r);
+                    }
                 }
                 const int m = min(32, nh - k0);
                 for (int k = 0; k < m; k++) {
@@ -772,18 +778,17 @@ __device__ __forceinline__ T exact_sum(Cx<NT_> &c, double cpre, double cs, doubl
                     for (int i0 = e0; i0 < e1; i0 += 64) {
                         const int m0 = min(32, e1 - i0), m1 = min(32, e1 - i0 - 32);
                         float ta = 0.f, tb = 0.f;
-                        if (c.lane < m0) ta = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + c.lane, r)));
-                        if (c.lane < m1) tb = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + 32 + c.lane, r)));
-#pragma unroll
-                        for (int i = 0; i < 32; i++) {
-                            const float t = __shfl_sync(0xffffffffu, ta, i);
-                            if (i < m0) s = F::add(s, (T)t);
+                        if (r == 0) {                       // my own tile (the walker is rank 0)
+                            if (c.lane < m0) ta = c.s_E[i0 + c.lane];
+                            if (c.lane < m1) tb = c.s_E[i0 + 32 + c.lane];
+                        } else {
+                            if (c.lane < m0) ta = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + c.lane, r)));
+                            if (c.lane < m1) tb = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + 32 + c.lane, r)));
                         }
-#pragma unroll
-                        for (int i = 0; i < 32; i++) {
-                            const float t = __shfl_sync(0xffffffffu, tb, i);
-                            if (i < m1) s = F::add(s, (T)t);
-                        }
+#pragma unroll 4
+                        for (int i = 0; i < m0; i++) s = F::add(s, (T)__shfl_sync(0xffffffffu, ta, i));
+#pragma unroll 4
+                        for (int i = 0; i < m1; i++) s = F::add(s, (T)__shfl_sync(0xffffffffu, tb, i));
                     }
                 }
             }
