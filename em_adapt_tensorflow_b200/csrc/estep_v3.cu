@@ -108,6 +108,59 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
                  ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// ---- tensor memory (TMEM) as a per-thread array: 32x32b shape, thread i of the warp <-> TMEM lane
+// (32 * (warp % 4) + i), one 32-bit column per element.  256 KB per SM that nothing else uses here.
+template <int COLS> __device__ __forceinline__ void tm_alloc(uint32_t *smem_result) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(smem_result)), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+template <int COLS> __device__ __forceinline__ void tm_dealloc(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "n"(COLS) : "memory");
+}
+__device__ __forceinline__ void tm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_ld8(uint32_t taddr, float (&v)[8]) {
+    uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7) : "r"(taddr) : "memory");
+    tm_wait_ld();
+    v[0] = __uint_as_float(r0); v[1] = __uint_as_float(r1); v[2] = __uint_as_float(r2); v[3] = __uint_as_float(r3);
+    v[4] = __uint_as_float(r4); v[5] = __uint_as_float(r5); v[6] = __uint_as_float(r6); v[7] = __uint_as_float(r7);
+}
+__device__ __forceinline__ float tm_ld1(uint32_t taddr) {
+    uint32_t r0;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n" : "=r"(r0) : "r"(taddr) : "memory");
+    tm_wait_ld();
+    return __uint_as_float(r0);
+}
+__device__ __forceinline__ void tm_st8(uint32_t taddr, const float (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};\n"
+                 ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+                   "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+                   "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])) : "memory");
+}
+__device__ __forceinline__ void tm_st1(uint32_t taddr, float v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};\n" ::"r"(taddr), "r"(__float_as_uint(v)) : "memory");
+}
+// visit my PPT plane elements (element j <-> tile pixel j * NT + tid), eight at a time
+template <int PPT, typename F> __device__ __forceinline__ void for_each_x(uint32_t tx, F &&f) {
+    constexpr int NC = PPT / 8;
+#pragma unroll
+    for (int ch = 0; ch < NC; ch++) {
+        float v[8];
+        tm_ld8(tx + ch * 8, v);
+#pragma unroll
+        for (int e = 0; e < 8; e++) f(ch * 8 + e, v[e]);
+    }
+#pragma unroll
+    for (int j = NC * 8; j < PPT; j++) f(j, tm_ld1(tx + j));
+}
+__host__ __device__ constexpr int tm_cols(int ppt) {          // 7 warps share a lane quarter: 7 * PPT columns, a power of two >= 32
+    return 7 * ppt <= 32 ? 32 : 7 * ppt <= 64 ? 64 : 7 * ppt <= 128 ? 128 : 7 * ppt <= 256 ? 256 : 512;
+}
+
 __device__ __forceinline__ unsigned long long gtimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
@@ -127,6 +180,7 @@ struct Misc {
     int hn[MAXC];
     uint64_t full_bar[NST];             // producers: stage filled (bulk-copy bytes landed)
     uint64_t e0_bar;                    // compute: E0 of my tile landed in shared memory
+    uint32_t tmem_base;                 // tcgen05.alloc result
     uint32_t pstat[2][NPW][8];          // producers -> compute: zero counts [0..3], largest margin [4] per warp
     uint64_t cmd_bar[2];                // compute -> producers: image of sequence parity q may be streamed
     uint64_t ready_bar[2];              // producers -> compute: planes of sequence parity q are in the scratch
@@ -189,6 +243,7 @@ template <int NT_> struct Cx {
     uint32_t xround;      // exchanges done (mailbox parity), identical in every CTA
     uint32_t hround;      // histogram rounds done (hist buffer parity)
     uint32_t csyncs;      // cluster syncs done (xbar index / parity)
+    uint32_t tx;          // TMEM address of my plane elements (lane quarter of my warp, my warp's columns)
     // per image
     int b, P;
     uint32_t mask;
@@ -838,23 +893,21 @@ template <int NT_> __device__ __forceinline__ SelScratch *sel(Cx<NT_> &c) { retu
 // one histogram round over my tile's margins E - x.  Zero margins (usually the largest single
 // bin by far) are counted with ballots instead of same-address shared atomics.
 template <int NT_, int PPT, bool WINDOW>
-__device__ __forceinline__ void hist_pass(Cx<NT_> &c, const float (&x)[PPT], uint32_t lo, uint32_t hi, int sh,
-                                          uint32_t *h) {
+__device__ __forceinline__ void hist_pass(Cx<NT_> &c, uint32_t lo, uint32_t hi, int sh, uint32_t *h) {
     for (int i = c.tid; i < NB2; i += NT_) h[i] = 0u;
     csync<NT_>();
     uint32_t zeros = 0u;
-#pragma unroll
-    for (int j = 0; j < PPT; j++) {
+    for_each_x<PPT>(c.tx, [&](int j, float xv) {
         const int i = j * NT_ + c.tid;
         const bool valid = i < c.n_t;
-        const uint32_t key = valid ? __float_as_uint(__fsub_rn(c.s_E[i], x[j])) : 0xffffffffu;
+        const uint32_t key = valid ? __float_as_uint(__fsub_rn(c.s_E[i], xv)) : 0xffffffffu;
         if (WINDOW) {
             zeros += (key == 0u) ? 1u : 0u;
             if (valid && key != 0u) atomicAdd(&h[win_bin(key, lo)], 1u);
         } else {
             if (valid && key >= lo && key <= hi) atomicAdd(&h[(key - lo) >> sh], 1u);
         }
-    }
+    });
     if (WINDOW) {
         zeros = __reduce_add_sync(0xffffffffu, zeros);
         if (c.lane == 0 && zeros) atomicAdd(&h[0], zeros);
@@ -969,7 +1022,7 @@ __device__ __forceinline__ uint32_t local_select(Cx<NT_> &c, const uint32_t *key
 // The value of rank k (0-based) among the margins E[i] - x[i] of the whole image.  *zeros receives
 // the exact number of zero margins when the first (windowed) round saw them (else 0xffffffff).
 template <int NT_, int PPT>
-__device__ __forceinline__ float select_margin(Cx<NT_> &c, const float (&x)[PPT], uint32_t k, uint32_t lo_key,
+__device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t k, uint32_t lo_key,
                                                uint32_t *zeros) {
     SelScratch *ss = sel(c);
     uint32_t lo = lo_key, hi = 0u, r = k;
@@ -978,8 +1031,8 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, const float (&x)[PPT]
     *zeros = 0xffffffffu;
     for (int guard = 0; guard < 6; guard++) {
         uint32_t *h = ss->hist[c.hround & 1u];
-        if (window) hist_pass<NT_, PPT, true>(c, x, lo, hi, sh, h);
-        else hist_pass<NT_, PPT, false>(c, x, lo, hi, sh, h);
+        if (window) hist_pass<NT_, PPT, true>(c, lo, hi, sh, h);
+        else hist_pass<NT_, PPT, false>(c, lo, hi, sh, h);
         const Located L = locate(c, r);
         if (L.bin < 0) {
             if (c.tid == 0) atomicExch(c.p->status, 200 + guard);
@@ -998,17 +1051,16 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, const float (&x)[PPT]
             // gather the candidates of the bin into every CTA, in rank order of the CTAs
             if (c.tid == 0) c.ms->lcount = 0u;
             csync<NT_>();
-#pragma unroll
-            for (int j = 0; j < PPT; j++) {
+            for_each_x<PPT>(c.tx, [&](int j, float xv) {
                 const int i = j * NT_ + c.tid;
                 if (i < c.n_t) {
-                    const uint32_t key = __float_as_uint(__fsub_rn(c.s_E[i], x[j]));
+                    const uint32_t key = __float_as_uint(__fsub_rn(c.s_E[i], xv));
                     if (key >= klo && key <= khi) {
                         const uint32_t pos = atomicAdd(&c.ms->lcount, 1u);
                         if (pos < (uint32_t)GCAP) ss->mylist[pos] = key;
                     }
                 }
-            }
+            });
             csync<NT_>();
             const int fb = L.bin & (SUBB - 1);
             const uint32_t mine = ss->fine[c.rank][fb];
@@ -1167,7 +1219,11 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
         }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
+    if (c.warp == 0) tm_alloc<tm_cols(PPT)>(&c.ms->tmem_base);
+    tm_fence_before();
     hw_cluster_sync();                                  // every CTA's barriers exist before any remote arrival
+    tm_fence_after();
+    c.tx = c.ms->tmem_base + ((uint32_t)(c.warp & 3) << 21) + (uint32_t)((c.warp >> 2) * PPT);   // lane 32*(warp%4), my columns
     if (c.tid >= NT_) {
         producer_main<NT_>(p, c.ms, staging, c.rank, slot, c.base, c.n_t);
         hw_cluster_sync();
@@ -1295,40 +1351,57 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
                     nsel++;
                     trc(c, 0, (seq << 8) | 7u);
                     trc(c, 2, ((uint32_t)j << 8) | (uint32_t)t);
-                    float x[PPT];
+                    // the class plane, with the biases the class received so far re-applied in order
+                    // (weaklabel.cpp:90-92), goes into tensor memory: element j of my thread = tile
+                    // pixel j * NT + tid.  The three passes of the selection read it from there.
                     float *plc = c.planes + (size_t)plane * p.Npad + c.base;
                     const int hn = c.ms->hn[plane];
+                    {
+                        constexpr int NC = PPT / 8;
 #pragma unroll
-                    for (int q = 0; q < PPT; q++) {
-                        const int i = q * NT_ + c.tid;
-                        x[q] = (i < c.n_t) ? __ldcg(plc + i) : 0.f;
-                    }
-                    for (int e = 0; e < hn; e++) {          // the biases the class received so far, in order
-                        const float hb = c.ms->hbias[plane][e];
+                        for (int ch = 0; ch < NC; ch++) {
+                            float v[8];
 #pragma unroll
-                        for (int q = 0; q < PPT; q++) x[q] = __fadd_rn(x[q], hb);
+                            for (int e = 0; e < 8; e++) {
+                                const int i = (ch * 8 + e) * NT_ + c.tid;
+                                v[e] = (i < c.n_t) ? __ldcg(plc + i) : 0.f;
+                            }
+                            for (int e2 = 0; e2 < hn; e2++) {
+                                const float hb = c.ms->hbias[plane][e2];
+#pragma unroll
+                                for (int e = 0; e < 8; e++) v[e] = __fadd_rn(v[e], hb);
+                            }
+                            tm_st8(c.tx + ch * 8, v);
+                        }
+#pragma unroll
+                        for (int j = NC * 8; j < PPT; j++) {
+                            const int i = j * NT_ + c.tid;
+                            float v = (i < c.n_t) ? __ldcg(plc + i) : 0.f;
+                            for (int e2 = 0; e2 < hn; e2++) v = __fadd_rn(v, c.ms->hbias[plane][e2]);
+                            tm_st1(c.tx + j, v);
+                        }
+                        tm_wait_st();
                     }
                     uint32_t e_top = (__float_as_uint(dmax_bound) >> 23) + 1u;
                     if (e_top > 254u) e_top = 254u;
                     const uint32_t lo_key = (e_top > (uint32_t)WIN_BINADES ? e_top - WIN_BINADES : 0u) << 23;
                     uint32_t zeros;
-                    bias = select_margin<NT_, PPT>(c, x, k, lo_key, &zeros);
+                    bias = select_margin<NT_, PPT>(c, k, lo_key, &zeros);
                     csync<NT_>();
                     if (bias != 0.f) {
                         // fold: x += bias (weaklabel.cpp:90-92), E = max(E, x) (:94-99)
                         const bool rewrite = (hn == HCAP);
                         uint32_t gained = 0u, znew = 0u;
-#pragma unroll
-                        for (int q = 0; q < PPT; q++) {
+                        for_each_x<PPT>(c.tx, [&](int q, float xv) {
                             const int i = q * NT_ + c.tid;
                             if (i < c.n_t) {
-                                const float xn = __fadd_rn(x[q], bias);
+                                const float xn = __fadd_rn(xv, bias);
                                 if (rewrite) __stcg(plc + i, xn);
                                 const float E = c.s_E[i];
                                 if (xn > E) { c.s_E[i] = xn; gained++; }
                                 if (xn >= E) znew++;
                             }
-                        }
+                        });
                         block_reduce_to_outbox(c, gained, znew, 0u, 0u, 0u, 0);
                         const uint32_t (*box)[MBW] = exchange(c, 2);
                         uint32_t gsum = 0u, zsum = 0u;
@@ -1387,6 +1460,8 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
         }
     }
     trc(c, 0, 0xEEEEu);
+    csync<NT_>();
+    if (c.warp == 0) tm_dealloc<tm_cols(PPT)>(c.ms->tmem_base);
     hw_cluster_sync();                                  // nobody leaves while a peer may still address its shared memory
     trc(c, 0, 0xFFFFu);
 }
