@@ -213,6 +213,7 @@ template <typename T, int NT_> struct SumScratch {
     int wany[32];
     int nheads;
     int pad[3];
+    alignas(16) float terms[64];        // the walker's staging of a chunk's terms
 };
 
 template <int NT_> struct Layout {
@@ -830,20 +831,30 @@ __device__ __forceinline__ T exact_sum(Cx<NT_> &c, double cpre, double cs, doubl
                     if (chunk_apply(fk, s)) continue;
                     // a crossing chunk (or a mispredicted segment): term by term
                     const int e0 = h0 * L, e1 = min((t0 + 1) * L, n_t_r);
+                    // The adds form one dependent chain.  The terms are staged in an aligned buffer and read
+                    // back four at a time (one shared-memory latency per four adds; a shuffle or a scalar
+                    // load per term would put its latency into the chain).
                     for (int i0 = e0; i0 < e1; i0 += 64) {
-                        const int m0 = min(32, e1 - i0), m1 = min(32, e1 - i0 - 32);
-                        float ta = 0.f, tb = 0.f;
-                        if (r == 0) {                       // my own tile (the walker is rank 0)
-                            if (c.lane < m0) ta = c.s_E[i0 + c.lane];
-                            if (c.lane < m1) tb = c.s_E[i0 + 32 + c.lane];
+                        const int m = min(64, e1 - i0);
+                        __syncwarp();
+                        if (r == 0) {                               // my own tile (the walker is rank 0)
+                            if (c.lane < m) ss->terms[c.lane] = c.s_E[i0 + c.lane];
+                            if (c.lane + 32 < m) ss->terms[c.lane + 32] = c.s_E[i0 + 32 + c.lane];
                         } else {
-                            if (c.lane < m0) ta = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + c.lane, r)));
-                            if (c.lane < m1) tb = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + 32 + c.lane, r)));
+                            if (c.lane < m) ss->terms[c.lane] = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + c.lane, r)));
+                            if (c.lane + 32 < m) ss->terms[c.lane + 32] = __uint_as_float(ld_peer(peer_addr(c.s_E + i0 + 32 + c.lane, r)));
                         }
-#pragma unroll 4
-                        for (int i = 0; i < m0; i++) s = F::add(s, (T)__shfl_sync(0xffffffffu, ta, i));
-#pragma unroll 4
-                        for (int i = 0; i < m1; i++) s = F::add(s, (T)__shfl_sync(0xffffffffu, tb, i));
+                        __syncwarp();
+                        const float4 *t4 = reinterpret_cast<const float4 *>(ss->terms);
+                        int i = 0;
+                        for (; i + 4 <= m; i += 4) {
+                            const float4 v = t4[i >> 2];
+                            s = F::add(s, (T)v.x);
+                            s = F::add(s, (T)v.y);
+                            s = F::add(s, (T)v.z);
+                            s = F::add(s, (T)v.w);
+                        }
+                        for (; i < m; i++) s = F::add(s, (T)ss->terms[i]);
                     }
                 }
             }
