@@ -25,9 +25,9 @@ launches)
       python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --parity-images 0 > gpurun_out/ncu_launches.log 2>&1
   echo "launches exit $?"; tail -12 gpurun_out/launches.csv ;;
 full)
-  timeout 600 python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 --images 64 > gpurun_out/plain_full.log 2>&1 &&
+  timeout 600 python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 --images 64 --path fast > gpurun_out/plain_full.log 2>&1 &&
   timeout 1200 ncu --set full --clock-control none --import-source on -k regex:estep -s 3 -c 1 -f -o gpurun_out/prof \
-      python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 --images 64 > gpurun_out/ncu_full.log 2>&1
+      python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 --images 64 --path fast > gpurun_out/ncu_full.log 2>&1
   echo "full exit $?"; tail -3 gpurun_out/ncu_full.log ;;
 esac
 done
