@@ -239,6 +239,7 @@ static int plan_geometry(weaklabel_plan *pl) {
     if (pl->geometry_ok) return WEAKLABEL_OK;
     const int N = pl->N;
     int G = pl->tune_G;
+    if (G == 9) G = 8;                                  // clusters of 9 exist for the warp-specialised kernel only
     if (G == 0) {
         G = 1;
         while (G < 8 && (N + G - 1) / G > TS_MAX) G *= 2;
@@ -275,7 +276,7 @@ static int plan_geometry(weaklabel_plan *pl) {
     pl->fG = 0;
     {
         const int cap = FAST_PPT_MAX * NT;
-        int fG = pl->tune_G;
+        int fG = pl->tune_G == 9 ? 8 : pl->tune_G;
         if (fG == 0) {
             fG = 1;
             while (fG < MAX_CLUSTER && (N + fG - 1) / fG > cap) fG *= 2;

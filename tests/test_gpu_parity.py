@@ -159,6 +159,22 @@ def test_fast_path_forced_geometries(name, tune, variant):
     assert got_map.tobytes() == want_map.tobytes()
 
 
+@pytest.mark.parametrize("name,tune", [("c3_321_b30", (0, 0, 2)), ("c3_321_b30", (0, 0, 7)), ("c4_513_b4", (9, 0, 1)),
+                                       ("c4_513_b4", (8, 0, 2)), ("c4_513_scale5", (9, 0, 1)), ("c2_41_b30", (9, 0, 3))])
+def test_warp_specialised_kernel_cycles_images(name, tune):
+    """estep_v3.cu with FEWER resident clusters than images: every cluster works through a queue of
+    images while its producer warps stream the next one (staging-ring reuse across images, both
+    plane sets of the scratch, command / ready hand-shake), incl. the non-portable cluster size 9."""
+    f, l, p = cases.build_case(name)
+    want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
+    for _ in range(2):
+        got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="fast")
+        assert bias_g.tobytes() == bias_o.tobytes()
+        assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
+        assert np.array_equal(got_lab, want_lab)
+        assert got_map.tobytes() == want_map.tobytes()
+
+
 def test_fast_path_refuses_what_it_does_not_cover():
     torch = _torch()
     f, l, p = cases.build_case("nosuppress_p3")
