@@ -504,13 +504,28 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 const float low = __fsub_rn(x, p.margin);
                 float a0 = -INFINITY, a1 = -INFINITY;
                 int k = 0;
+                if (p.C == 21) {                        // the VOC class count: fully unrolled
+                    float a2 = -INFINITY;
+#pragma unroll
+                    for (int kk = 0; kk < 21; kk += 3) {
+                        const float t0 = px[kk], t1 = px[kk + 1], t2 = px[kk + 2];
+                        const float u0 = (kk == pl0) ? -INFINITY : (t0 > x ? low : t0);
+                        const float u1 = (kk + 1 == pl0) ? -INFINITY : (t1 > x ? low : t1);
+                        const float u2 = (kk + 2 == pl0) ? -INFINITY : (t2 > x ? low : t2);
+                        a0 = fmaxf(a0, u0);
+                        a1 = fmaxf(a1, u1);
+                        a2 = fmaxf(a2, u2);
+                    }
+                    a0 = fmaxf(a0, a2);
+                    k = p.C;                            // both generic loops below are empty
+                }
                 for (; k + 1 < pl0; k += 2) {
                     const float t0 = px[k], t1 = px[k + 1];
                     a0 = fmaxf(a0, t0 > x ? low : t0);
                     a1 = fmaxf(a1, t1 > x ? low : t1);
                 }
                 if (k < pl0) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
-                k = pl0 + 1;
+                k = max(k, pl0 + 1);
                 for (; k + 1 < p.C; k += 2) {
                     const float t0 = px[k], t1 = px[k + 1];
                     a0 = fmaxf(a0, t0 > x ? low : t0);
@@ -1350,6 +1365,15 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
 
         trc(c, 0, (seq << 8) | 6u);
         // 4. iterations (weaklabel.cpp:82-101)
+        // The zero-margin lower bounds only pay when quotas leave slack (a class that keeps more pixels
+        // than its quota is skipped without a selection).  When the quotas of the label set add up to
+        // the whole image every step selects anyway: the per-fold exchange that maintains them is dropped.
+        bool track_zeros;
+        {
+            long long quota = 0;
+            for (int k = 0; k < c.P; k++) quota += (c.ms->plist[k] == 0) ? p.nth_bg : p.nth_fg;
+            track_zeros = quota < (long long)p.N - (p.N >> 6);
+        }
         const uint8_t *ord = p.order + (size_t)c.b * p.num_iter * p.C;
         uint32_t nsel = 0;
         for (int j = 0; j < p.num_iter; j++) {
@@ -1413,13 +1437,17 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v3_kernel(const __gri
                                 if (xn >= E) znew++;
                             }
                         });
-                        block_reduce_to_outbox(c, gained, znew, 0u, 0u, 0u, 0);
-                        const uint32_t (*box)[MBW] = exchange(c, 2);
-                        uint32_t gsum = 0u, zsum = 0u;
-                        for (int q = 0; q < c.G; q++) { gsum += box[q][0]; zsum += box[q][1]; }
-                        if (c.tid < c.P) {
-                            const uint32_t z = c.ms->zlb[c.tid];
-                            c.ms->zlb[c.tid] = (c.tid == plane) ? zsum : (z > gsum ? z - gsum : 0u);
+                        if (track_zeros) {
+                            block_reduce_to_outbox(c, gained, znew, 0u, 0u, 0u, 0);
+                            const uint32_t (*box)[MBW] = exchange(c, 2);
+                            uint32_t gsum = 0u, zsum = 0u;
+                            for (int q = 0; q < c.G; q++) { gsum += box[q][0]; zsum += box[q][1]; }
+                            if (c.tid < c.P) {
+                                const uint32_t z = c.ms->zlb[c.tid];
+                                c.ms->zlb[c.tid] = (c.tid == plane) ? zsum : (z > gsum ? z - gsum : 0u);
+                            }
+                        } else if (c.tid < c.P) {
+                            c.ms->zlb[c.tid] = 0u;                      // a valid lower bound without the exchange
                         }
                         if (c.tid == 0) {
                             if (rewrite) { c.ms->hn[plane] = 0; }
