@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout -k 5 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "cycles_images" > gpurun_out/pytest_cyc.log 2>&1; echo "pytest exit $?"; tail -5 gpurun_out/pytest_cyc.log
+WEAKLABEL_V3_TRAIL=1 timeout -k 5 200 python bench.py --steps 1 --warmup 0 --no-cpu --no-e2e --parity-images 0 > gpurun_out/e.json 2> gpurun_out/e.err; echo "exit $?"
+grep "^trail" gpurun_out/e.err > gpurun_out/trail_t.txt; wc -l gpurun_out/trail_t.txt
