@@ -161,6 +161,17 @@ __host__ __device__ constexpr int tm_cols(int ppt) {          // 7 warps share a
     return 7 * ppt <= 32 ? 32 : 7 * ppt <= 64 ? 64 : 7 * ppt <= 128 ? 128 : 7 * ppt <= 256 ? 256 : 512;
 }
 
+// L2 policy for the score stream: every byte is read exactly once, so its lines should be the first to
+// leave the L2 (the plane scratch, which is re-read for the whole select chain, should stay)
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;\n" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
 __device__ __forceinline__ unsigned long long gtimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
@@ -414,6 +425,7 @@ struct Prod {
     int pw, lane;
     int base, n_t;
     uint32_t nbase;           // chunks of earlier images (stage and parity of chunk q: from nbase + q)
+    uint64_t pol;             // L2 evict-first policy of the score stream
 };
 
 __device__ __forceinline__ void prod_prefetch(const Prod &w, const float *img, int q) {
@@ -423,7 +435,7 @@ __device__ __forceinline__ void prod_prefetch(const Prod &w, const float *img, i
     const uintptr_t a0 = (uintptr_t)(img + (long long)(w.base + q * cpx) * p.C);
     const uintptr_t lo = (a0 + 15u) & ~(uintptr_t)15u, hi = (a0 + (uintptr_t)npx * p.C * 4u) & ~(uintptr_t)15u;
     if (hi > lo)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(lo), "r"((uint32_t)(hi - lo)) : "memory");
+        asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;\n" ::"l"(lo), "r"((uint32_t)(hi - lo)), "l"(w.pol) : "memory");
 }
 
 // called by a whole warp: copy chunk q of the tile into its stage, prefetch chunk q + PF_AHEAD
@@ -453,7 +465,7 @@ __device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int 
     if (w.lane == 0) {
         if (bytes) {
             mbar_expect_tx(bar, bytes);
-            bulk_g2s(stage + lead + nh, g0 + nh, bytes, bar);
+            bulk_g2s_hint(stage + lead + nh, g0 + nh, bytes, bar, w.pol);
         } else {
             mbar_arrive(bar);
         }
@@ -620,6 +632,7 @@ __device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, un
     w.base = base;
     w.n_t = n_t;
     w.nbase = 0;
+    w.pol = l2_evict_first_policy();
     for (uint32_t s = 0;; s++) {
         const int q = s & 1u;
         if (p.trail && w.lane == 0) p.trail[blockIdx.x * 32 + 12 + w.pw] = (s << 8) | 1u;
