@@ -44,26 +44,51 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _link(path, target):
+    """Create/refresh a symlink atomically; several ranks may do this at the same time."""
+    try:
+        if os.path.islink(path) and os.readlink(path) == target:
+            return
+        tmp = "%s.%d.tmp" % (path, os.getpid())
+        if os.path.lexists(tmp):
+            os.remove(tmp)
+        os.symlink(target, tmp)
+        os.replace(tmp, path)
+    except OSError:
+        if not os.path.lexists(path):
+            raise
+
+
 def build(force=False, verbose=False):
-    """Compile (if stale) and return the path of libweaklabel_cuda.so."""
+    """Compile (if stale) and return the path of libweaklabel_cuda.so.  Safe to call from several
+    processes at once (one rank per GPU): the compile is serialised by a lock file."""
+    os.makedirs(LIBDIR, exist_ok=True)
     if force or _stale():
-        os.makedirs(LIBDIR, exist_ok=True)
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-              ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
-        if verbose:
-            print(" ".join(cmd))
-        res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-        if verbose or res.returncode != 0:
-            sys.stderr.write(res.stdout)
-        if res.returncode != 0:
-            raise RuntimeError("nvcc failed building libweaklabel_cuda.so")
+        import fcntl
+        with open(os.path.join(LIBDIR, ".build.lock"), "w") as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            try:
+                if force or _stale():               # another process may have built it meanwhile
+                    tmp = "%s.%d.tmp" % (LIB, os.getpid())
+                    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+                          ["-o", tmp] + [os.path.join(CSRC, s) for s in SOURCES]
+                    if verbose:
+                        print(" ".join(cmd))
+                    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                    if verbose or res.returncode != 0:
+                        sys.stderr.write(res.stdout)
+                    if res.returncode != 0:
+                        if os.path.exists(tmp):
+                            os.remove(tmp)
+                        raise RuntimeError("nvcc failed building libweaklabel_cuda.so")
+                    os.replace(tmp, LIB)
+            finally:
+                fcntl.flock(lock, fcntl.LOCK_UN)
     drop = os.path.join(LIBDIR, "dropin")
     for name in DROPIN_NAMES:
         path = os.path.join(drop, name)
         os.makedirs(os.path.dirname(path), exist_ok=True)
-        if os.path.lexists(path):
-            os.remove(path)
-        os.symlink(os.path.relpath(LIB, os.path.dirname(path)), path)
+        _link(path, os.path.relpath(LIB, os.path.dirname(path)))
     return LIB
 
 
