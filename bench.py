@@ -261,7 +261,8 @@ def main():
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        os.environ.pop("NCCL_DEBUG", None)     # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        os.environ["NCCL_DEBUG_FILE"] = os.devnull
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
 
