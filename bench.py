@@ -374,7 +374,7 @@ def main():
                                 l2="inputs 5.66 GB per GPU >> 126 MB L2 (no flush needed)",
                                 parallelism="image-sharded x%d, no collective" % world),
                     roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                                  traffic=ncu_traffic(), kernel={"fast": "estep_v3_kernel", "fast2": "estep_v2_kernel", "fast1": "estep_fast_kernel", "generic": "estep_cluster_kernel"}.get(plan.last_path, "?"),
+                                  traffic=ncu_traffic(), kernel={"fast": "estep_v4_kernel", "fast3": "estep_v3_kernel", "fast2": "estep_v2_kernel", "fast1": "estep_fast_kernel", "generic": "estep_cluster_kernel"}.get(plan.last_path, "?"),
                                   alg_bytes_per_pixel=ALG_BYTES_PER_PIXEL, kernel_ms=k_ms, peak_source=peak_src),
                     cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clocks, parity=parity)
         print(json.dumps(line), flush=True)

@@ -203,6 +203,7 @@ struct weaklabel_plan {
     int tune_nt;                                    // v2 threads per CTA (0 auto, 512, 1024)
     V2Config v2; bool v2_ok; int v2_slots;          // second-generation kernel (estep_v2.cu)
     V3Config v3; bool v3_ok; int v3_slots;          // third-generation kernel (estep_v3.cu), tune_path 4
+    V4Config v4; bool v4_ok; int v4_slots;          // fourth-generation kernel (estep_v4.cu), tune_path 5 (the default)
     unsigned long long *d_prof; bool prof_on;       // [B][8] phase time stamps
     bool geometry_ok;
     int scratch_slots;
@@ -316,6 +317,16 @@ static int plan_geometry(weaklabel_plan *pl) {
         if (vs < 1) vs = 1;
         pl->v3_slots = vs;
     }
+    pl->v4_ok = (pl->tune_nt == 0) && v4_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, &pl->v4);
+    if (pl->v4_ok) {
+        int vs = pl->tune_slots ? pl->tune_slots : pl->v4.max_clusters;
+        if (vs > pl->v4.max_clusters) vs = pl->v4.max_clusters;
+        if (vs > pl->B) vs = pl->B;
+        if (vs < 1) vs = 1;
+        pl->v4_slots = vs;
+    }
+    if (pl->tune_path == 5 && !pl->v4_ok)
+        return fail(WEAKLABEL_ERR_ARG, "the fourth-generation fast path cannot hold %d pixels with this cluster/tile tuning", N);
     if (pl->tune_path == 2 && !pl->v2_ok)
         return fail(WEAKLABEL_ERR_ARG, "the fast path cannot hold %d pixels with this cluster/tile tuning", N);
     if (pl->tune_path == 4 && !pl->v3_ok)
@@ -325,6 +336,7 @@ static int plan_geometry(weaklabel_plan *pl) {
     int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
     if (pl->v2_ok && pl->v2_slots > ss) ss = pl->v2_slots;
     if (pl->v3_ok && 2 * pl->v3_slots > ss) ss = 2 * pl->v3_slots;      // two plane sets per resident cluster
+    if (pl->v4_ok && 2 * pl->v4_slots > ss) ss = 2 * pl->v4_slots;
     pl->scratch_slots = ss;
     CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 2) * pl->Npad * sizeof(float)));
     CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)ss * pl->Npad));
@@ -395,7 +407,7 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
 extern "C" WL_API long long weaklabel_plan_launches(const weaklabel_plan *pl) { return pl ? pl->launches : 0; }
 
 extern "C" WL_API int weaklabel_plan_set_path(weaklabel_plan *pl, int path) {
-    if (!pl || path < 0 || path > 4) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2 (second-generation fast), 3 (first-generation fast) or 4 (warp-specialised fast)");
+    if (!pl || path < 0 || path > 5) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2..4 (earlier generations of the fast kernel) or 5 (fast)");
     pl->tune_path = path;
     return WEAKLABEL_OK;
 }
@@ -523,6 +535,10 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     const bool v2_ok = pl->v2_ok && cond_ok;
     const bool fast1_ok = pl->fG > 0 && cond_ok;
     const bool v3_ok = pl->v3_ok && cond_ok;
+    const bool v4_ok = pl->v4_ok && cond_ok;
+    if (pl->tune_path == 5 && !v4_ok)
+        return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
+                    "contiguous pixels)");
     if (pl->tune_path == 4 && !v3_ok)
         return fail(WEAKLABEL_ERR_ARG, "warp-specialised fast path forced but not applicable (needs suppress_others, "
                     "margin >= 0, contiguous pixels)");
@@ -531,7 +547,7 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
                     "contiguous pixels)");
     if (pl->tune_path == 3 && !fast1_ok)
         return fail(WEAKLABEL_ERR_ARG, "first-generation fast path forced but not applicable");
-    const int path = pl->tune_path ? pl->tune_path : (v3_ok ? 4 : (v2_ok ? 2 : 1));
+    const int path = pl->tune_path ? pl->tune_path : (v4_ok ? 5 : (v3_ok ? 4 : (v2_ok ? 2 : 1)));
     int slots_used = pl->slots;
     p.Npad = pl->Npad; p.sub_px = pl->sub_px;
     if (path == 2) {
@@ -542,6 +558,15 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
         slots_used = pl->v3_slots;
         const char *pf = getenv("WEAKLABEL_V3_PREFETCH");          // tuning knob: chunks of L2 prefetch distance
         p.pf_ahead = pf ? atoi(pf) : V3_PF_AHEAD;
+        p.trail = debug_trail();
+    } else if (path == 5) {
+        p.TS = pl->v4.TS; p.ntiles = pl->v4.G; p.L = pl->v4.L; p.G = pl->v4.G; p.sub_px = pl->v4.cpx;
+        p.se_floats = pl->v4.se_floats;
+        slots_used = pl->v4_slots;
+        const char *pf = getenv("WEAKLABEL_V3_PREFETCH");          // tuning knob: chunks of L2 prefetch distance
+        p.pf_ahead = pf ? atoi(pf) : V3_PF_AHEAD;
+        const char *fl = getenv("WEAKLABEL_V4_FLAGS");             // A/B switches (estep_kernel.cuh: V4_F_*)
+        p.flags = fl ? atoi(fl) : 0;
         p.trail = debug_trail();
     } else if (path == 3) {
         p.TS = pl->fTS; p.ntiles = (pl->N + pl->fTS - 1) / pl->fTS; p.L = pl->fL; p.G = pl->fG;
@@ -555,8 +580,9 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
     p.prof = pl->prof_on ? pl->d_prof : nullptr;
     CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
-    if (path != 2 && path != 4) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
-    if (path == 4) CUDA_TRY(launch_estep_v3(p, pl->v3, slots_used, st));
+    if (path != 2 && path != 4 && path != 5) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
+    if (path == 5) CUDA_TRY(launch_estep_v4(p, pl->v4, slots_used, st));
+    else if (path == 4) CUDA_TRY(launch_estep_v3(p, pl->v3, slots_used, st));
     else if (path == 2) CUDA_TRY(launch_estep_v2(p, pl->v2, slots_used, st));
     else if (path == 3) CUDA_TRY(launch_estep_fast(p, slots_used, st));
     else CUDA_TRY(launch_estep(p, slots_used, st));

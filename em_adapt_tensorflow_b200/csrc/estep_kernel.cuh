@@ -60,7 +60,19 @@ struct EStepParams {
     double *shift;            // [B]  (double)mean0 - mean1
     unsigned long long *prof; // [B][8] phase time stamps (globaltimer ns) or NULL
     volatile unsigned int *trail;  // v3 debugging: [CTA][16] progress words in mapped host memory, or NULL
+    // v4
+    int se_floats;            // floats of the running-max tile in shared memory (>= TS and >= NT * L)
+    int flags;                // V4_F_* switches (A/B runs and bisection; 0 = everything on)
+    unsigned long long *prof2; // [B][32] fine-grained phase accumulators (ns) or NULL
 };
+
+// v4 switches: a set bit turns the named optimisation OFF (falls back to the simpler code path)
+constexpr int V4_F_NO_RANKCOUNT = 1;      // local selection always by histogram rounds
+constexpr int V4_F_NO_RESIDENT = 2;       // evict the class plane after every step (no TMEM residency across steps)
+constexpr int V4_F_NO_FASTLABEL = 4;      // every pixel takes the exact (double) label path
+constexpr int V4_F_LOOSE_ZEROS = 8;       // first-generation zero-count bound (counts every pixel above the old max)
+constexpr int V4_F_NO_DIGEST = 16;        // sums: the walker fetches every segment from its owner (no pushed digests)
+constexpr int V4_F_CLASSIC_XCHG = 32;     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
 
 size_t estep_smem_bytes();
 cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream);
@@ -97,6 +109,14 @@ constexpr int V3_PPT_MAX = 37;
 struct V3Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
 bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out);
 cudaError_t launch_estep_v3(const EStepParams &p, const V3Config &cfg, int n_clusters, cudaStream_t stream);
+
+// fourth-generation kernel (estep_v4.cu): quad (float4) pixel ownership, two class planes resident in
+// tensor memory, branch-free histogram pass, st.async exchanges, digest-based order-exact sums
+constexpr int V4_NT = 896;
+constexpr int V4_MAXG = 9;
+struct V4Config { int nt, qpt, G, TS, L, cpx, se_floats, max_clusters; };
+bool v4_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V4Config *out);
+cudaError_t launch_estep_v4(const EStepParams &p, const V4Config &cfg, int n_clusters, cudaStream_t stream);
 
 struct FinalizeParams {
     float *map; long long s0, s2;

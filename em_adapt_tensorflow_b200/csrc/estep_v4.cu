@@ -1,0 +1,1916 @@
+// estep_v4.cu -- the E-step kernel of the common configuration, fourth generation (sm_100a).
+//
+// Contract (unchanged from the third generation): one thread-block cluster per image, persistent,
+// images claimed from a counter; suppress_others = true with a margin >= 0, contiguous pixels, the
+// image fits the cluster.  Warp-specialised: NT compute threads + NPW producer warps per CTA.  The
+// producers stream the 84-byte score vectors of image t+1 through a bulk-copy ring while the compute
+// threads run the selection chain of image t (weaklabel.cpp:82-101).
+//
+// What is new, all of it on the compute side (the kernel was latency-bound there):
+//   * QUAD OWNERSHIP.  A thread owns whole quads of four consecutive pixels (quad q = k * NT + tid):
+//     the running max E ("extrenum", weaklabel.cpp:67-77) is read and written as float4 from shared
+//     memory, a class plane moves as float4 between the L2 scratch and tensor memory, and four
+//     consecutive TMEM columns are one tcgen05.ld/st.x4.  Padding pixels carry E = 0, x = -inf, so that
+//     no pass needs a validity test per element (their margin is +inf: the largest key, never selected).
+//   * TWO PLANES RESIDENT IN TENSOR MEMORY (512 columns = two slots): label sets of one or two classes
+//     (63 % of VOC-style batches) never reload a plane and never replay a bias history; larger sets use
+//     the two slots as a cache with write-back, so a plane in the scratch is always current.
+//   * A BRANCH-FREE HISTOGRAM PASS (10 instructions per margin instead of 28): 2048 bins = zero bin,
+//     one bin below the window, 128 bins per binade over the 15 binades under the largest possible
+//     margin; zero margins go to a private counter per warp instead of one contended bin.
+//   * EXCHANGES BY st.async: every CTA stores its words straight into the mailboxes of its peers with the
+//     completion counted in bytes on the receiver's mbarrier -- no release fence, no second barrier.
+//   * THE ZERO-MARGIN BOUND IS TIGHT: a fold only takes pixels away from the other classes where the
+//     folded class was NOT the maximum before (plus a bound on exact ties), so a class that still owns
+//     more than its quota is skipped without a selection (the previous bound counted every pixel the
+//     folded class already owned and forced one or two useless selections per image).
+//   * ORDER-EXACT SUMS BY DIGEST (weaklabel.cpp:69-80, 102-106): every CTA condenses its tile into a
+//     few composite functions (seqsum.cuh) plus the terms of the rare binade-crossing chunks and pushes
+//     this digest to CTA 0 with one bulk copy; two warps of CTA 0 walk the float and the double sum at
+//     the same time out of their own shared memory.  mean_max_0's digest is formed at the start of the
+//     image (E0 is still in shared memory) and costs no cluster round trip of its own.
+//   * LABELS IN FLOAT: argmax over the final scores; only pixels whose best two scores are within the
+//     rounding distance of the re-centring shift (weaklabel.cpp:108-112) take the exact double path.
+#include <float.h>
+#include <math.h>
+#include "estep_kernel.cuh"
+#include "seqsum.cuh"
+
+namespace wl {
+namespace v4 {
+
+constexpr int NB = 2048;                // histogram bins
+constexpr int NSB = 64;                 // super bins exchanged through the mailboxes
+constexpr int SUBB = NB / NSB;          // 32 fine bins per super bin
+constexpr int WIN_SH = 16;              // 128 bins per binade inside the window
+constexpr int WIN_BINADES = 15;
+constexpr int GCAP = 1024;              // candidates gathered into every CTA
+constexpr int RCMAX = 256;              // up to here the local selection ranks by counting
+constexpr int MBW = 72;                 // mailbox words per CTA per exchange (a multiple of 4)
+constexpr int HT = 512;                 // threads that scan a 2048-bin histogram (4 bins each)
+constexpr int MAXG = V4_MAXG;
+constexpr int NPW = 4;                  // producer warps per CTA
+constexpr int NST = 8;                  // stages of the staging ring (a multiple of NPW: a stage always belongs
+                                        // to the same warp, which then sees its mbarrier phases in order)
+constexpr int STAGE_BYTES = 7168;
+constexpr int EAGER_P = 4;              // planes whose zero counts are formed by the producers
+constexpr int DIG_SEG = 8;              // segments of a pushed digest
+constexpr int DIG_CROSS = 3;            // binade-crossing chunks whose terms travel with the digest
+constexpr int DIG_L = 44;               // terms per crossing chunk (>= the longest chunk)
+constexpr int BIG_SEG = 64;             // segments of the local digest
+constexpr unsigned long long WAIT_LIMIT_NS = 4000000000ull;   // a wait gives up after 4 s (status + trap instead of a hung GPU)
+static_assert(NST % NPW == 0, "a stage must always belong to the same producer warp");
+static_assert(MBW % 4 == 0 && NSB <= MBW, "mailbox rows are moved as 16-byte vectors");
+
+// ---------------------------------------------------------------------------------------------
+// PTX helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void hw_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n"
+                 "barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+template <int NT_> __device__ __forceinline__ void csync() {       // the compute threads of this CTA
+    asm volatile("bar.sync 1, %0;\n" ::"n"(NT_) : "memory");
+}
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t peer_addr(const void *local_smem, int rank) {
+    uint32_t a = smem_u32(local_smem), r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(a), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_peer(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;\n" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_peer(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared::cluster.u32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+// remote store whose completion is counted (in bytes) on an mbarrier of the SAME remote CTA
+__device__ __forceinline__ void st_async_u32(uint32_t addr, uint32_t v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];\n"
+                 ::"r"(addr), "r"(v), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void st_async_u64(uint32_t addr, unsigned long long v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u64 [%0], %1, [%2];\n"
+                 ::"r"(addr), "l"(v), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void st_async_v4(uint32_t addr, uint4 v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.u32 [%0], {%1,%2,%3,%4}, [%5];\n"
+                 ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar) : "memory");
+}
+// shared memory of this CTA -> shared memory of a peer, completion on the peer's mbarrier
+__device__ __forceinline__ void bulk_s2peer(uint32_t peer_dst, const void *src, uint32_t bytes, uint32_t peer_bar) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+                 ::"r"(peer_dst), "r"(smem_u32(src)), "r"(bytes), "r"(peer_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {     // arrive + expect
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {           // release.cta
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_peer(uint32_t cluster_addr) {   // release at cluster scope
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+    return t;
+}
+// Every wait is bounded: a lost arrival ends in a trap with a status code instead of a hung GPU.
+__device__ __noinline__ void wait_failed(const EStepParams *p, int code) {
+    atomicExch(p->status, code);
+    if (p->trail) p->trail[blockIdx.x * 32 + 30] = (unsigned int)code | (threadIdx.x << 16);
+    __threadfence_system();
+    __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, const EStepParams *status, int code) {  // acquire.cta
+    const uint32_t a = smem_u32(bar);
+    uint32_t ok;
+    unsigned long long t0 = 0ull;
+    for (;;) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if (ok) break;
+        const unsigned long long t = gtimer();          // a failed try_wait has already slept for a while
+        if (t0 == 0ull) t0 = t;
+        else if (t - t0 > WAIT_LIMIT_NS) wait_failed(status, code);
+    }
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t *bar, uint32_t parity, const EStepParams *status, int code) {  // acquire.cluster
+    const uint32_t a = smem_u32(bar);
+    uint32_t ok;
+    unsigned long long t0 = 0ull;
+    for (;;) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if (ok) break;
+        const unsigned long long t = gtimer();
+        if (t0 == 0ull) t0 = t;
+        else if (t - t0 > WAIT_LIMIT_NS) wait_failed(status, code);
+    }
+}
+// global -> shared bulk copy (16-byte aligned on both sides, size a multiple of 16), completion on bar
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;\n" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+// ---- tensor memory as a per-thread array: 32x32b shape, thread i of the warp <-> TMEM lane
+// (32 * (warp % 4) + i), one 32-bit column per element; four consecutive columns = one quad of pixels.
+__device__ __forceinline__ void tm_alloc512(uint32_t *smem_result) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;\n" ::"r"(smem_u32(smem_result)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tm_dealloc512(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ float4 tm_ld4(uint32_t taddr) {
+    uint32_t r0, r1, r2, r3;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(taddr) : "memory");
+    tm_wait_ld();
+    return make_float4(__uint_as_float(r0), __uint_as_float(r1), __uint_as_float(r2), __uint_as_float(r3));
+}
+__device__ __forceinline__ void tm_ld8(uint32_t taddr, float4 &a, float4 &b) {
+    uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7) : "r"(taddr) : "memory");
+    tm_wait_ld();
+    a = make_float4(__uint_as_float(r0), __uint_as_float(r1), __uint_as_float(r2), __uint_as_float(r3));
+    b = make_float4(__uint_as_float(r4), __uint_as_float(r5), __uint_as_float(r6), __uint_as_float(r7));
+}
+__device__ __forceinline__ void tm_st4(uint32_t taddr, float4 v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};\n"
+                 ::"r"(taddr), "r"(__float_as_uint(v.x)), "r"(__float_as_uint(v.y)), "r"(__float_as_uint(v.z)),
+                   "r"(__float_as_uint(v.w)) : "memory");
+}
+// columns of one plane slot: 7 warps share a lane quarter, 4 * QPT columns each
+__host__ __device__ constexpr int slot_cols(int qpt) { return 28 * qpt <= 256 ? 256 : 512; }
+__host__ __device__ constexpr int n_slots(int qpt) { return 512 / slot_cols(qpt); }
+
+// ---------------------------------------------------------------------------------------------
+// shared memory
+// ---------------------------------------------------------------------------------------------
+// One segment of a tile's digest: the action on the running sum of the chunks [head, tail] of the tile
+// (chunk t = terms [t * L, (t + 1) * L)).  kind 1: m -> m + a[m & 1] while the exponent field is e
+// (seqsum.cuh); kind 0: add the terms one by one (cslot >= 0: they travel with the digest).
+struct alignas(16) DigEntry {
+    unsigned long long e;
+    long long a0, a1;
+    int kind;
+    int cslot;
+    int nterms;
+    uint16_t head, tail;
+    uint32_t pad[2];
+};
+static_assert(sizeof(DigEntry) == 48, "DigEntry layout");
+struct alignas(16) Digest {                 // what a CTA pushes to CTA 0 (fixed size)
+    int nseg, ncross, pad0, pad1;
+    DigEntry seg[DIG_SEG];
+    float cross[DIG_CROSS][DIG_L];
+};
+static_assert(sizeof(Digest) % 16 == 0, "digests move by bulk copy");
+struct alignas(16) BigDigest {              // the local digest of a tile
+    int nseg, total, pad0, pad1;
+    DigEntry seg[BIG_SEG];
+};
+
+struct alignas(16) Misc {
+    alignas(16) uint32_t outbox[2][MBW];    // alternating with the exchanges
+    double wscr_d[32];
+    uint32_t wscr_u[32];
+    uint32_t wred[32][8];
+    uint32_t zlb[MAXC];                 // zero-margin count per plane: exact or a lower bound
+    uint64_t full_bar[NST];             // producers: stage filled (bulk-copy bytes landed)
+    uint64_t e0_bar;                    // compute: E0 of my tile landed in shared memory
+    uint64_t cmd_bar[2];                // compute -> producers: image of sequence parity q may be streamed
+    uint64_t ready_bar[2];              // producers -> compute: planes of sequence parity q are in the scratch
+    uint64_t xbar[2];                   // exchanges: bytes of the peers' st.async (alternating)
+    uint64_t sbar[2];                   // plain cluster sync of the compute threads (alternating)
+    uint64_t dig_bar;                   // CTA 0: the peers' digests landed
+    uint64_t res_bar;                   // the two sums landed
+    unsigned long long sumres[2];       // [0] float sum bits, [1] double sum bits
+    uint32_t tmem_base;                 // tcgen05.alloc result
+    uint32_t pstat[2][NPW][8];          // producers -> compute: zero counts [0..3], largest margin [4], ties [5]
+    int cmd_img[2];                     // image index of the command (>= B: stop)
+    double bc_d;
+    uint32_t bc_u;
+    int sel_S;
+    uint32_t sel_preS;
+    int sel_bin;
+    uint32_t sel_pre, sel_cnt;
+    uint32_t sel_key;
+    uint32_t lcount;
+    uint32_t wcnt[32];
+    uint32_t wfirst[32];
+    float state0;                       // CTA 0: float running sum at the end of its own tile
+    uint8_t plist[MAXC];
+    uint8_t pplist[NPW][MAXC];          // the producers' copy (image t+1)
+};
+
+constexpr int NBX = NB + 32;             // + one private zero-margin counter per warp
+struct SelScratch {
+    alignas(16) uint32_t hist[2][NBX];  // rotating per histogram round; peers read 32 fine bins
+    uint32_t lhist[NB];                 // CTA-local selection among gathered candidates
+    alignas(16) uint32_t gather[GCAP + 4];
+    uint32_t mylist[GCAP];
+    uint32_t fine[MAXG][SUBB];
+};
+
+template <typename T> struct ScanItem {     // what the segmented scan carries
+    ChunkFn<T> f;
+    int hidx;
+    int flag;
+};
+// Aliases SelScratch.  Only `inbound` (written in CTA 0 at the END of an image) may overlap the two
+// histograms, which the selections expect to be zero: they are cleared at the start of every image.
+struct alignas(16) SumScratch {
+    Digest inbound[MAXG][2];            // CTA 0: [tile][0 float, 1 double]
+    BigDigest big;
+    ScanItem<double> wagg[32];
+    ChunkFn<double> wlast[32];
+};
+static_assert(sizeof(Digest) * MAXG * 2 >= sizeof(uint32_t) * 2 * NBX, "the local digest must not overlap the histograms");
+
+template <int NT_> struct Layout {
+    static __host__ __device__ constexpr size_t A16(size_t x) { return (x + 15) / 16 * 16; }
+    static __host__ __device__ constexpr size_t uni_bytes() {
+        size_t b = A16(sizeof(SelScratch)), c = A16(sizeof(SumScratch));
+        return b > c ? b : c;
+    }
+    static constexpr size_t MBOX_BYTES = 2 * MAXG * MBW * 4;
+    static constexpr size_t STAGING_BYTES = (size_t)NST * STAGE_BYTES;
+    static size_t total(int se_floats) {
+        return A16((size_t)se_floats * 4) + MBOX_BYTES + A16(sizeof(Misc)) + uni_bytes() + 2 * A16(sizeof(Digest)) + STAGING_BYTES;
+    }
+};
+
+template <int NT_> struct Cx {
+    const EStepParams *p;
+    int tid, lane, warp, rank, G;
+    float *planes;        // scratch of the image in work: [C+2][Npad]
+    float *absmax;        // plane C of the scratch (single foreground class only)
+    uint8_t *absidx;
+    float *s_E;
+    uint32_t (*mbox)[MAXG][MBW];
+    Misc *ms;
+    unsigned char *uni;
+    Digest *outd;         // [2]: my float and double digests (pushed to CTA 0)
+    int base, n_t, TQ;    // my tile: pixels [base, base + n_t), TQ = quads that hold a pixel
+    uint32_t xround;      // exchanges done (mailbox / outbox / barrier parity), identical in every CTA
+    uint32_t hround;      // histogram rounds done (hist buffer parity)
+    uint32_t csyncs;      // plain cluster syncs done
+    uint32_t tm;          // TMEM address of my lane quarter, my warp's first column of slot 0
+    // per image
+    int b, P;
+    uint32_t mask;
+    int first_absent;
+    int res0, res1;       // plane resident in each TMEM slot (-1: none); scalars: an indexed array would
+    bool dirty0, dirty1;  // push the whole context into local memory
+    int mru;
+};
+
+template <int NT_> __device__ __forceinline__ void trc(const Cx<NT_> &c, int k, uint32_t v) {
+    if (c.p->trail && c.tid == 0) c.p->trail[blockIdx.x * 32 + k] = v;
+}
+template <int NT_> __device__ __forceinline__ SelScratch *sel(Cx<NT_> &c) { return reinterpret_cast<SelScratch *>(c.uni); }
+template <int NT_> __device__ __forceinline__ SumScratch *sums(Cx<NT_> &c) { return reinterpret_cast<SumScratch *>(c.uni); }
+
+// Plain cluster-wide barrier of the COMPUTE threads: every CTA arrives on the barrier of every CTA
+// (release at cluster scope after a CTA barrier), then waits on its own.  Two barriers alternate.
+template <int NT_>
+__device__ __forceinline__ void cluster_sync_compute(Cx<NT_> &c) {
+    csync<NT_>();
+    if (c.G > 1) {
+        uint64_t *bar = &c.ms->sbar[c.csyncs & 1u];
+        if (c.tid < c.G) mbar_arrive_peer(peer_addr(bar, c.tid));
+        mbar_wait_cluster(bar, (c.csyncs >> 1) & 1u, c.p, 401);
+        c.csyncs++;
+    }
+}
+
+// The outbox of the current exchange (written by any compute threads before exchange()).
+template <int NT_> __device__ __forceinline__ uint32_t *outbox(Cx<NT_> &c) { return c.ms->outbox[c.xround & 1u]; }
+
+// Every CTA hands the first n words of its outbox to every CTA of the cluster (itself included);
+// returns the mailbox that now holds them: box[p][w] = word w of CTA p.
+//
+// st.async path: thread 0 arms the barrier (one arrival + the bytes expected from all G senders) BEFORE
+// the CTA barrier after which this CTA sends, so no peer can complete this exchange and send data of
+// the next one (which goes to the other barrier / mailbox / outbox) before this barrier is armed.
+template <int NT_>
+__device__ __forceinline__ const uint32_t (*exchange(Cx<NT_> &c, int n))[MBW] {
+    Misc *s = c.ms;
+    const uint32_t par = c.xround & 1u;
+    if (c.G > 1) {
+        const int nv = (n + 3) >> 2;
+        if (c.p->flags & V4_F_CLASSIC_XCHG) {
+            csync<NT_>();
+            for (int i = c.tid; i < c.G * n; i += NT_) {
+                const int peer = i / n, w = i - peer * n;
+                st_peer(peer_addr(&c.mbox[par][c.rank][w], peer), s->outbox[par][w]);
+            }
+            cluster_sync_compute(c);
+        } else {
+            if (c.tid == 0) mbar_expect_tx(&s->xbar[par], (uint32_t)(c.G * nv * 16));
+            csync<NT_>();
+            for (int i = c.tid; i < c.G * nv; i += NT_) {
+                const int peer = i / nv, v = i - peer * nv;
+                const uint4 w = *reinterpret_cast<const uint4 *>(&s->outbox[par][4 * v]);
+                st_async_v4(peer_addr(&c.mbox[par][c.rank][4 * v], peer), w, peer_addr(&s->xbar[par], peer));
+            }
+            mbar_wait(&s->xbar[par], (c.xround >> 1) & 1u, c.p, 402);
+        }
+    } else {
+        csync<NT_>();
+        for (int w = c.tid; w < n; w += NT_) c.mbox[par][0][w] = s->outbox[par][w];
+        csync<NT_>();
+    }
+    c.xround++;
+    return c.mbox[par];
+}
+
+template <int NT_>
+__device__ __forceinline__ uint32_t block_excl_scan_u32(Cx<NT_> &c, uint32_t v, uint32_t *total) {
+    constexpr int NW = NT_ / 32;
+    uint32_t inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (c.lane >= o) inc += t;
+    }
+    if (c.lane == 31) c.ms->wscr_u[c.warp] = inc;
+    csync<NT_>();
+    if (c.warp == 0) {
+        uint32_t w = c.lane < NW ? c.ms->wscr_u[c.lane] : 0u, winc = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (c.lane >= o) winc += t;
+        }
+        c.ms->wscr_u[c.lane] = winc - w;          // exclusive warp offsets
+        if (c.lane == 31) c.ms->bc_u = winc;
+    }
+    csync<NT_>();
+    uint32_t r = c.ms->wscr_u[c.warp] + inc - v;
+    *total = c.ms->bc_u;
+    csync<NT_>();
+    return r;
+}
+
+// exclusive prefix of a double over the compute threads; *total = the sum (two CTA barriers)
+template <int NT_>
+__device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, double *total) {
+    constexpr int NW = NT_ / 32;
+    double inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        double t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (c.lane >= o) inc += t;
+    }
+    if (c.lane == 31) c.ms->wscr_d[c.warp] = inc;
+    csync<NT_>();
+    // every warp scans the warp totals itself (NW <= 32 values): no second hand-over
+    double w = c.lane < NW ? c.ms->wscr_d[c.lane] : 0.0, winc = w;
+    for (int o = 1; o < 32; o <<= 1) {
+        double t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (c.lane >= o) winc += t;
+    }
+    const double wex = __shfl_sync(0xffffffffu, winc - w, c.warp);
+    *total = __shfl_sync(0xffffffffu, winc, 31);
+    csync<NT_>();                                 // wscr_d may be rewritten
+    return wex + (inc - v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// producers: HBM -> (L2 prefetch) -> staging ring (bulk copy) -> compact planes + E0 plane in the
+// L2 scratch, zero-margin counts, tie count and the largest possible margin of my tile
+// ---------------------------------------------------------------------------------------------
+struct Prod {
+    const EStepParams *p;
+    Misc *ms;
+    unsigned char *staging;   // NST stages shared by the producer warps
+    int pw, lane;
+    int base, n_t;
+    uint32_t nbase;           // chunks of earlier images (stage and parity of chunk q: from nbase + q)
+    uint64_t pol;             // L2 evict-first policy of the score stream
+};
+
+__device__ __forceinline__ void prod_prefetch(const Prod &w, const float *img, int q) {
+    const EStepParams &p = *w.p;
+    const int cpx = p.sub_px;
+    const int npx = min(cpx, w.n_t - q * cpx);
+    const uintptr_t a0 = (uintptr_t)(img + (long long)(w.base + q * cpx) * p.C);
+    const uintptr_t lo = (a0 + 15u) & ~(uintptr_t)15u, hi = (a0 + (uintptr_t)npx * p.C * 4u) & ~(uintptr_t)15u;
+    if (hi > lo)
+        asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;\n" ::"l"(lo), "r"((uint32_t)(hi - lo)), "l"(w.pol) : "memory");
+}
+
+// called by a whole warp: copy chunk q of the tile into its stage, prefetch chunk q + pf_ahead
+__device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int q, int nchunks) {
+    const EStepParams &p = *w.p;
+    const int cpx = p.sub_px;
+    const int npx = min(cpx, w.n_t - q * cpx);
+    const int nfl = npx * p.C;
+    const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
+    const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
+    const int d = (int)((w.nbase + (uint32_t)q) % NST);
+    float *stage = reinterpret_cast<float *>(w.staging + (size_t)d * STAGE_BYTES);
+    const int nh = lead ? min(4 - lead, nfl) : 0;               // floats before the first aligned 16 bytes
+    const uint32_t bytes = (uint32_t)((nfl - nh) * 4) & ~15u;   // aligned interior
+    const int t0 = nh + (int)(bytes >> 2);                      // first float of the ragged tail
+    uint64_t *bar = &w.ms->full_bar[d];
+    if (w.lane >= 1 && w.lane <= 3) {
+        const int f = w.lane - 1;
+        if (f < nh) stage[lead + f] = __ldg(g0 + f);
+    } else if (w.lane >= 4 && w.lane <= 6) {
+        const int f = t0 + (w.lane - 4);
+        if (f < nfl) stage[lead + f] = __ldg(g0 + f);
+    } else if (w.lane == 7) {
+        if (q + p.pf_ahead < nchunks && p.pf_ahead > 0) prod_prefetch(w, img, q + p.pf_ahead);
+    }
+    __syncwarp();                                               // ragged stores before the arrival (release)
+    if (w.lane == 0) {
+        if (bytes) {
+            mbar_expect_tx(bar, bytes);
+            bulk_g2s_hint(stage + lead + nh, g0 + nh, bytes, bar, w.pol);
+        } else {
+            mbar_arrive(bar);
+        }
+    }
+}
+
+// one image: chunks q with (nbase + q) % NPW == pw of the CTA's tile
+__device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *planes, uint8_t *absidx) {
+    const EStepParams &p = *w.p;
+    const ImageMeta *im = p.meta + b;
+    const int P = im->P;
+    uint8_t *pl = w.ms->pplist[w.pw];
+    if (w.lane < MAXC) pl[w.lane] = im->plist[w.lane];
+    __syncwarp();
+    const int pl0 = pl[0], pl1 = pl[1], pl2 = pl[2], pl3 = pl[3];
+    const int first_absent = im->first_absent;
+    const float *img = p.map + (long long)b * p.s0;
+    const int cpx = p.sub_px;
+    const int nchunks = (w.n_t + cpx - 1) / cpx;
+    // a single FOREGROUND class: an absent class of lower index (the background) can win a rounding tie,
+    // so the suppressed absent maximum is kept.  A background-only image needs nothing: every absent class
+    // has a higher index and a suppressed score <= the background's (weaklabel.cpp:45-65).
+    const bool need_abs = (P == 1) && (P < p.C) && (pl0 != 0);
+    float *absmax = planes + (size_t)p.C * p.Npad;
+    float *e0pl = planes + (size_t)(p.C + 1) * p.Npad;
+    uint32_t zc0 = 0u, zc1 = 0u, zc2 = 0u, zc3 = 0u, ties = 0u;
+    float dmx = 0.f;
+    const int q0 = (int)((w.pw + NPW - (w.nbase % NPW)) % NPW);   // my first chunk
+    // every stage is free (the producers met after the previous image): fill the ring, warm the L2
+    for (int q = q0; q < nchunks && q < max(NST, p.pf_ahead); q += NPW) {
+        if (q < NST) prod_issue(w, img, q, nchunks);
+        else if (w.lane == 0) prod_prefetch(w, img, q);
+    }
+    for (int q = q0; q < nchunks; q += NPW) {
+        const uint32_t n = w.nbase + (uint32_t)q;
+        const int d = (int)(n % NST);
+        mbar_wait(&w.ms->full_bar[d], (n / NST) & 1u, &p, 410);
+        const float *stage = reinterpret_cast<const float *>(w.staging + (size_t)d * STAGE_BYTES);
+        const int npx = min(cpx, w.n_t - q * cpx);
+        const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
+        const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
+        const int i0 = w.base + q * cpx;
+        float *out = planes + i0;
+        if (need_abs) {
+            for (int gt = w.lane; gt < npx; gt += 32) {
+                const float *px = stage + lead + gt * p.C;
+                const float x = px[pl0];
+                const float low = __fsub_rn(x, p.margin);
+                float a0 = -INFINITY, a1 = -INFINITY;
+                int k = 0;
+                for (; k + 1 < pl0; k += 2) {
+                    const float t0 = px[k], t1 = px[k + 1];
+                    a0 = fmaxf(a0, t0 > x ? low : t0);
+                    a1 = fmaxf(a1, t1 > x ? low : t1);
+                }
+                if (k < pl0) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
+                k = max(k, pl0 + 1);
+                for (; k + 1 < p.C; k += 2) {
+                    const float t0 = px[k], t1 = px[k + 1];
+                    a0 = fmaxf(a0, t0 > x ? low : t0);
+                    a1 = fmaxf(a1, t1 > x ? low : t1);
+                }
+                if (k < p.C) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
+                const float amax = fmaxf(a0, a1);
+                float tf = px[first_absent];
+                if (tf > x) tf = low;
+                float E = FLT_MIN;
+                if (x > E) E = x;
+                __stcg(out + gt, x);
+                __stcg(e0pl + i0 + gt, E);
+                __stcg(absmax + i0 + gt, amax);
+                absidx[i0 + gt] = (uint8_t)((tf == amax) ? first_absent : 254);
+                zc0 += (x == E) ? 1u : 0u;
+                dmx = fmaxf(dmx, __fsub_rn(E, x));
+            }
+        } else if (P <= 4) {
+            for (int gt = w.lane; gt < npx; gt += 32) {
+                const float *px = stage + lead + gt * p.C;
+                const float v0 = px[pl0];
+                const float v1 = (P > 1) ? px[pl1] : v0;
+                const float v2 = (P > 2) ? px[pl2] : v0;
+                const float v3 = (P > 3) ? px[pl3] : v0;
+                float E = FLT_MIN, mn = FLT_MAX;
+                if (v0 > E) E = v0;
+                if (v0 < mn) mn = v0;
+                if (v1 > E) E = v1;
+                if (v1 < mn) mn = v1;
+                if (v2 > E) E = v2;
+                if (v2 < mn) mn = v2;
+                if (v3 > E) E = v3;
+                if (v3 < mn) mn = v3;
+                __stcg(out + gt, v0);
+                if (P > 1) __stcg(out + (size_t)p.Npad + gt, v1);
+                if (P > 2) __stcg(out + 2 * (size_t)p.Npad + gt, v2);
+                if (P > 3) __stcg(out + 3 * (size_t)p.Npad + gt, v3);
+                __stcg(e0pl + i0 + gt, E);
+                const uint32_t e0 = (v0 == E) ? 1u : 0u, e1 = (P > 1 && v1 == E) ? 1u : 0u;
+                const uint32_t e2 = (P > 2 && v2 == E) ? 1u : 0u, e3 = (P > 3 && v3 == E) ? 1u : 0u;
+                zc0 += e0; zc1 += e1; zc2 += e2; zc3 += e3;
+                ties += (e0 + e1 + e2 + e3 >= 2u) ? 1u : 0u;
+                dmx = fmaxf(dmx, __fsub_rn(E, mn));
+            }
+        } else {
+            for (int gt = w.lane; gt < npx; gt += 32) {
+                const float *px = stage + lead + gt * p.C;
+                float E = FLT_MIN, mn = FLT_MAX;
+                for (int k = 0; k < P; k++) {
+                    const float v = px[pl[k]];
+                    __stcg(out + (size_t)k * p.Npad + gt, v);
+                    if (v > E) E = v;
+                    if (v < mn) mn = v;
+                }
+                __stcg(e0pl + i0 + gt, E);
+                uint32_t at = 0u;
+                for (int k = 0; k < P; k++) at += (px[pl[k]] == E) ? 1u : 0u;
+                zc0 += (px[pl0] == E) ? 1u : 0u;
+                zc1 += (px[pl1] == E) ? 1u : 0u;
+                zc2 += (px[pl2] == E) ? 1u : 0u;
+                zc3 += (px[pl3] == E) ? 1u : 0u;
+                ties += (at >= 2u) ? 1u : 0u;
+                dmx = fmaxf(dmx, __fsub_rn(E, mn));
+            }
+        }
+        __syncwarp();                                  // stage drained by every lane
+        if (q + NST < nchunks) prod_issue(w, img, q + NST, nchunks);
+    }
+    w.nbase += (uint32_t)nchunks;
+    // my share of the tile's statistics
+    uint32_t dm = __float_as_uint(dmx);               // margins are >= +0: the bit patterns order like the values
+    for (int o = 16; o; o >>= 1) {
+        zc0 += __shfl_xor_sync(0xffffffffu, zc0, o);
+        zc1 += __shfl_xor_sync(0xffffffffu, zc1, o);
+        zc2 += __shfl_xor_sync(0xffffffffu, zc2, o);
+        zc3 += __shfl_xor_sync(0xffffffffu, zc3, o);
+        ties += __shfl_xor_sync(0xffffffffu, ties, o);
+        dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
+    }
+    if (w.lane == 0) {
+        uint32_t *st = w.ms->pstat[par][w.pw];
+        st[0] = zc0; st[1] = zc1; st[2] = zc2; st[3] = zc3; st[4] = dm; st[5] = ties;
+    }
+}
+
+template <int NT_>
+__device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, unsigned char *staging, int slot, int base, int n_t) {
+    Prod w;
+    w.p = &p;
+    w.ms = ms;
+    w.pw = (int)(threadIdx.x - NT_) >> 5;
+    w.lane = threadIdx.x & 31;
+    w.staging = staging;
+    w.base = base;
+    w.n_t = n_t;
+    w.nbase = 0;
+    w.pol = l2_evict_first_policy();
+    for (uint32_t s = 0;; s++) {
+        const int q = s & 1u;
+        mbar_wait(&ms->cmd_bar[q], (s >> 1) & 1u, &p, 411);
+        const int b = *reinterpret_cast<volatile int *>(&ms->cmd_img[q]);
+        if (b >= p.B) break;
+        float *planes = p.planes + (size_t)(slot * 2 + q) * (size_t)(p.C + 2) * p.Npad;
+        uint8_t *absidx = p.absent_idx + (size_t)(slot * 2 + q) * p.Npad;
+        asm volatile("bar.sync 2, %0;\n" ::"n"(NPW * 32) : "memory");   // every stage of the ring is drained
+        prod_image(w, b, q, planes, absidx);
+        __threadfence();                                        // my plane/E0 stores have reached the L2 (the
+        __syncwarp();                                           // E0 tile is fetched from there by the copy engine)
+        if (w.lane == 0) mbar_arrive(&ms->ready_bar[q]);        // release: planes and statistics of my chunks
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// order-exact running sums (weaklabel.cpp:69-80 float, :102-106 double) by digest
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct FnIO;
+template <> struct FnIO<float> {
+    static __device__ __forceinline__ ChunkFn<float> shfl(const ChunkFn<float> &f, int src) {
+        ChunkFn<float> g;
+        g.e = __shfl_sync(0xffffffffu, f.e, src);
+        g.a0 = __shfl_sync(0xffffffffu, f.a0, src);
+        g.a1 = __shfl_sync(0xffffffffu, f.a1, src);
+        g.kind = __shfl_sync(0xffffffffu, f.kind, src);
+        return g;
+    }
+    static __device__ __forceinline__ ChunkFn<float> shfl_up(const ChunkFn<float> &f, int d) {
+        ChunkFn<float> g;
+        g.e = __shfl_up_sync(0xffffffffu, f.e, d);
+        g.a0 = __shfl_up_sync(0xffffffffu, f.a0, d);
+        g.a1 = __shfl_up_sync(0xffffffffu, f.a1, d);
+        g.kind = __shfl_up_sync(0xffffffffu, f.kind, d);
+        return g;
+    }
+    static __device__ __forceinline__ ChunkFn<double> widen(const ChunkFn<float> &f) {
+        ChunkFn<double> g;
+        g.e = f.e; g.a0 = f.a0; g.a1 = f.a1; g.kind = f.kind;
+        return g;
+    }
+    static __device__ __forceinline__ ChunkFn<float> narrow(const ChunkFn<double> &f) {
+        ChunkFn<float> g;
+        g.e = (uint32_t)f.e; g.a0 = (int32_t)f.a0; g.a1 = (int32_t)f.a1; g.kind = f.kind;
+        return g;
+    }
+};
+template <> struct FnIO<double> {
+    static __device__ __forceinline__ ChunkFn<double> shfl(const ChunkFn<double> &f, int src) {
+        ChunkFn<double> g;
+        g.e = (uint64_t)__shfl_sync(0xffffffffu, (unsigned long long)f.e, src);
+        g.a0 = (int64_t)__shfl_sync(0xffffffffu, (long long)f.a0, src);
+        g.a1 = (int64_t)__shfl_sync(0xffffffffu, (long long)f.a1, src);
+        g.kind = __shfl_sync(0xffffffffu, f.kind, src);
+        return g;
+    }
+    static __device__ __forceinline__ ChunkFn<double> shfl_up(const ChunkFn<double> &f, int d) {
+        ChunkFn<double> g;
+        g.e = (uint64_t)__shfl_up_sync(0xffffffffu, (unsigned long long)f.e, d);
+        g.a0 = (int64_t)__shfl_up_sync(0xffffffffu, (long long)f.a0, d);
+        g.a1 = (int64_t)__shfl_up_sync(0xffffffffu, (long long)f.a1, d);
+        g.kind = __shfl_up_sync(0xffffffffu, f.kind, d);
+        return g;
+    }
+    static __device__ __forceinline__ ChunkFn<double> widen(const ChunkFn<double> &f) { return f; }
+    static __device__ __forceinline__ ChunkFn<double> narrow(const ChunkFn<double> &f) { return f; }
+};
+
+// Tolerance (relative to the binade) inside which a predicted binade boundary is not trusted: the
+// float running sum drifts from the real sum by accumulated rounding (a few hundred ulps at most
+// here), the double one practically not at all.  Only speed depends on it, never the result.
+template <typename T> struct drift_tol;
+template <> struct drift_tol<float> { static constexpr double value = 1.0 / 8192.0; };
+template <> struct drift_tol<double> { static constexpr double value = 1.0 / 1073741824.0; };
+
+// per-thread chunk sums in double (the prediction of seqsum.cuh); returns my chunk's exclusive
+// prefix inside the tile, *tile_total = the tile's sum.  s_E is zero beyond the tile.
+template <int NT_>
+__device__ __forceinline__ double chunk_prefix(Cx<NT_> &c, double *tile_total, double *chunk_sum) {
+    const int L = c.p->L;
+    const float *t = c.s_E + c.tid * L;
+    double a0 = 0.0, a1 = 0.0;
+    int i = 0;
+    for (; i + 1 < L; i += 2) { a0 += (double)t[i]; a1 += (double)t[i + 1]; }
+    if (i < L) a0 += (double)t[i];
+    const double cs = a0 + a1;
+    *chunk_sum = cs;
+    return block_excl_scan_f64(c, cs, tile_total);
+}
+
+// The local digest of my tile for the sum of type T over the terms in s_E: maximal runs of chunks
+// summarised for the same binade become one composite (segmented scan over the tile); chunks that
+// contain, or are suspiciously close to, a binade crossing stay singletons that are added term by
+// term.  `before` = the (double) sum of the tiles of lower rank; cpre / cs from chunk_prefix.
+template <typename T, int NT_>
+__device__ __forceinline__ void build_big_digest(Cx<NT_> &c, double cpre, double cs, double before) {
+    typedef fp_traits<T> F;
+    typedef FnIO<T> IO;
+    constexpr int NW = NT_ / 32;
+    Misc *ms = c.ms;
+    SumScratch *ss = sums(c);
+    BigDigest *big = &ss->big;
+    const int L = c.p->L;
+    const int c0 = c.tid * L;
+    const int len = max(0, min(L, c.n_t - c0));
+    const double pin = before + cpre;
+    ChunkFn<T> f = (len > 0) ? chunk_eval<T>(c.s_E + c0, len, pin) : chunk_identity<T>();
+    if (f.kind == 1) {
+        // distrust predictions that pass close to a boundary of the binade
+        const double lo = (double)F::from(f.e), tol = lo * drift_tol<T>::value;
+        if (pin - lo < tol || (lo + lo) - (pin + cs) < tol) f.kind = 0;
+    }
+    if (c.p->flags & V4_F_NO_DIGEST) { if (f.kind == 1) f.kind = 0; }
+    // segment heads: the chunk before me (warp edges through shared memory)
+    ChunkFn<T> pv = IO::shfl_up(f, 1);
+    if (c.lane == 31) ss->wlast[c.warp] = IO::widen(f);
+    csync<NT_>();
+    if (c.lane == 0 && c.warp > 0) pv = IO::narrow(ss->wlast[c.warp - 1]);
+    bool head;
+    if (f.kind == 2) head = false;
+    else if (c.tid == 0 || f.kind == 0) head = true;
+    else head = (pv.kind != 1) || (pv.e != f.e);
+    // segmented inclusive scan inside the warp; hidx = chunk index of the head of my segment
+    ChunkFn<T> x = f;
+    int hidx = c.tid;
+    bool flag = head;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const ChunkFn<T> y = IO::shfl_up(x, d);
+        const int yh = __shfl_up_sync(0xffffffffu, hidx, d);
+        const bool yf = __shfl_up_sync(0xffffffffu, flag ? 1 : 0, d) != 0;
+        if (c.lane >= d && !flag) {
+            if (y.kind != 2) hidx = yh;
+            x = chunk_compose(y, x);
+            flag = yf;
+        }
+    }
+    if (c.lane == 31) { ss->wagg[c.warp].f = IO::widen(x); ss->wagg[c.warp].hidx = hidx; ss->wagg[c.warp].flag = flag ? 1 : 0; }
+    if (c.lane == 0) ms->wfirst[c.warp] = head ? 1u : 0u;
+    csync<NT_>();
+    {
+        // every warp scans the warp aggregates itself; carry INTO warp w = inclusive result of warp w-1
+        ChunkFn<T> v = c.lane < NW ? IO::narrow(ss->wagg[c.lane].f) : chunk_identity<T>();
+        int vh = c.lane < NW ? ss->wagg[c.lane].hidx : 0;
+        bool vf = c.lane < NW ? ss->wagg[c.lane].flag != 0 : false;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const ChunkFn<T> y = IO::shfl_up(v, d);
+            const int yh = __shfl_up_sync(0xffffffffu, vh, d);
+            const bool yf = __shfl_up_sync(0xffffffffu, vf ? 1 : 0, d) != 0;
+            if (c.lane >= d && !vf) {
+                if (y.kind != 2) vh = yh;
+                v = chunk_compose(y, v);
+                vf = yf;
+            }
+        }
+        const int src = c.warp > 0 ? c.warp - 1 : 0;
+        ChunkFn<T> cin = IO::shfl(v, src);
+        const int cinh = __shfl_sync(0xffffffffu, vh, src);
+        if (c.warp == 0) cin = chunk_identity<T>();
+        if (!flag) {                                  // no head at or before me inside my warp
+            if (cin.kind != 2) hidx = cinh;
+            x = chunk_compose(cin, x);
+        }
+    }
+    // tails: the chunk after me starts a segment (or I am the last chunk)
+    bool next_head = __shfl_down_sync(0xffffffffu, head ? 1 : 0, 1) != 0;
+    if (c.lane == 31) next_head = (c.warp + 1 < NW) ? (ms->wfirst[c.warp + 1] != 0u) : true;
+    const bool emit = next_head && x.kind != 2;
+    const uint32_t bal = __ballot_sync(0xffffffffu, emit);
+    if (c.lane == 0) ms->wcnt[c.warp] = (uint32_t)__popc(bal);
+    csync<NT_>();
+    {
+        uint32_t cnt = c.lane < NW ? ms->wcnt[c.lane] : 0u, inc = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (c.lane >= o) inc += t;
+        }
+        const uint32_t woff = __shfl_sync(0xffffffffu, inc - cnt, c.warp);
+        const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+        if (emit) {
+            const uint32_t id = woff + (uint32_t)__popc(bal & ((1u << c.lane) - 1u));
+            if (id < (uint32_t)BIG_SEG) {
+                DigEntry e;
+                e.e = (unsigned long long)x.e;
+                e.a0 = (long long)x.a0;
+                e.a1 = (long long)x.a1;
+                e.kind = x.kind == 1 ? 1 : 0;
+                e.cslot = -1;
+                e.nterms = 0;
+                e.head = (uint16_t)hidx;
+                e.tail = (uint16_t)c.tid;
+                e.pad[0] = e.pad[1] = 0u;
+                if (id == (uint32_t)BIG_SEG - 1u && total > (uint32_t)BIG_SEG) {   // overflow: the rest of the tile, term by term
+                    e.kind = 0;
+                    e.tail = (uint16_t)(NT_ - 1);
+                }
+                big->seg[id] = e;
+            }
+        }
+        if (c.tid == 0) { big->nseg = (int)min(total, (uint32_t)BIG_SEG); big->total = (int)total; }
+    }
+    csync<NT_>();
+}
+
+// warp 0: condense the local digest into the fixed-size digest that travels to CTA 0
+template <int NT_>
+__device__ __forceinline__ void compact_digest(Cx<NT_> &c, Digest *out) {
+    const BigDigest *big = &sums(c)->big;
+    const int L = c.p->L;
+    const int n = big->nseg;
+    int nseg = n;
+    if (n > DIG_SEG) nseg = DIG_SEG;
+    int ncross = 0;
+    for (int i0 = 0; i0 < nseg; i0 += 32) {
+        const int i = i0 + c.lane;
+        DigEntry e;
+        bool inl = false;
+        if (i < nseg) {
+            e = big->seg[i];
+            if (i == DIG_SEG - 1 && n > DIG_SEG) { e.kind = 0; e.tail = (uint16_t)(NT_ - 1); }
+            inl = (e.kind == 0) && (e.head == e.tail) && !(c.p->flags & V4_F_NO_DIGEST);
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, inl);
+        if (i < nseg) {
+            if (inl) {
+                const int slot = ncross + __popc(bal & ((1u << c.lane) - 1u));
+                if (slot < DIG_CROSS) {
+                    e.cslot = slot;
+                    e.nterms = max(0, min(L, c.n_t - (int)e.head * L));
+                }
+            }
+            out->seg[i] = e;
+        }
+        ncross += __popc(bal);
+    }
+    if (c.lane == 0) { out->nseg = nseg; out->ncross = min(ncross, DIG_CROSS); out->pad0 = out->pad1 = 0; }
+    __syncwarp();
+    // the terms of the crossing chunks
+    for (int i = 0; i < nseg; i++) {
+        const int slot = out->seg[i].cslot;
+        if (slot >= 0) {
+            const int t0 = (int)out->seg[i].head * L, nt = out->seg[i].nterms;
+            for (int j = c.lane; j < DIG_L; j += 32) out->cross[slot][j] = (j < nt) ? c.s_E[t0 + j] : 0.f;
+        }
+    }
+    __syncwarp();
+}
+
+// add terms one by one: `get(j)` delivers term j (any lane may be asked for any j, uniformly)
+template <typename T, typename G>
+__device__ __forceinline__ T add_range(T s, int i0, int i1, int lane, G &&get) {
+    typedef fp_traits<T> F;
+    for (int j0 = i0; j0 < i1; j0 += 32) {
+        const int j = j0 + lane;
+        const float v = (j < i1) ? get(j) : 0.f;                 // + 0 leaves a sum >= 0 unchanged
+#pragma unroll
+        for (int l = 0; l < 32; l++) s = F::add(s, (T)__shfl_sync(0xffffffffu, v, l));
+    }
+    return s;
+}
+
+// Walk the entries of one digest (all lanes of the warp hold the same state s).  `get(j)` = term j of
+// the tile the digest describes (used for raw ranges and for composites that do not apply).
+template <typename T, typename G>
+__device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, const float (*cross)[DIG_L],
+                                         int L, int n_t, int lane, const float *local, G &&get) {
+    typedef fp_traits<T> F;
+    for (int i = 0; i < nseg; i++) {
+        const DigEntry e = seg[i];
+        if (e.kind == 1) {
+            ChunkFn<T> f;
+            f.e = (typename F::U)e.e;
+            f.a0 = (typename F::S)e.a0;
+            f.a1 = (typename F::S)e.a1;
+            f.kind = 1;
+            if (chunk_apply(f, s)) continue;
+        }
+        if (e.kind == 0 && e.cslot >= 0 && cross != nullptr) {
+            const float4 *t4 = reinterpret_cast<const float4 *>(cross[e.cslot]);
+            const int m = e.nterms;
+            int j = 0;
+            for (; j + 4 <= m; j += 4) {
+                const float4 v = t4[j >> 2];
+                s = F::add(s, (T)v.x);
+                s = F::add(s, (T)v.y);
+                s = F::add(s, (T)v.z);
+                s = F::add(s, (T)v.w);
+            }
+            for (; j < m; j++) s = F::add(s, (T)cross[e.cslot][j]);
+            continue;
+        }
+        const int i0 = (int)e.head * L, i1 = min(((int)e.tail + 1) * L, n_t);
+        if (local != nullptr) {
+            // my own tile: the terms come straight out of shared memory (the loads do not depend on the
+            // running sum, so they are issued ahead of the add chain)
+            int j = i0;
+#pragma unroll 1
+            for (; j + 8 <= i1; j += 8) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) v[u] = local[j + u];
+#pragma unroll
+                for (int u = 0; u < 8; u++) s = F::add(s, (T)v[u]);
+            }
+            for (; j < i1; j++) s = F::add(s, (T)local[j]);
+        } else {
+            s = add_range<T>(s, i0, i1, lane, get);
+        }
+    }
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// binning of a margin key (bit pattern of a float >= +0) and the inverse
+//   bin 0: zero margins; bin 1: below the window; bins 2 .. : 128 per binade from lo_key; 2047: above
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int win_bin(uint32_t key, int base) {
+    int b = (int)(key >> WIN_SH) - base;
+    b = max(b, (int)min(key, 1u));
+    return min(b, NB - 1);
+}
+__device__ __forceinline__ void win_range(uint32_t bin, uint32_t lo_key, uint32_t &klo, uint32_t &khi) {
+    if (bin == 0u) { klo = khi = 0u; return; }
+    if (bin == 1u) { klo = 1u; khi = lo_key > 1u ? lo_key - 1u : 1u; return; }
+    klo = lo_key + ((bin - 2u) << WIN_SH);
+    khi = bin == (uint32_t)NB - 1u ? 0xffffffffu : klo + ((1u << WIN_SH) - 1u);
+    if (klo == 0u) klo = 1u;                            // lo_key == 0: key 0 belongs to bin 0, not to the first window bin
+}
+
+struct Located {
+    int bin;              // -1: inconsistent (NaN in the scores)
+    uint32_t pre, cnt;    // keys of the histogram below the bin / inside it
+};
+
+// the quads of a thread: k-th quad = tile quad k * NT + tid, TMEM columns [4k, 4k+4) of the slot.
+// tcgen05.ld/st are warp-collective: they are issued for EVERY k by every lane; quads beyond the
+// tile (q >= TQ) hold -inf and f must not touch shared/global memory for them.
+template <int NT_, int QPT, typename F>
+__device__ __forceinline__ void for_each_quad(Cx<NT_> &c, uint32_t ta, F &&f) {
+#pragma unroll
+    for (int k = 0; k + 1 < QPT; k += 2) {
+        float4 a, b;
+        tm_ld8(ta + 4 * k, a, b);
+        f(k, k * NT_ + c.tid, a);
+        f(k + 1, (k + 1) * NT_ + c.tid, b);
+    }
+    if (QPT & 1) {
+        constexpr int k = QPT - 1;
+        f(k, k * NT_ + c.tid, tm_ld4(ta + 4 * k));
+    }
+}
+
+// one histogram round over my tile's margins E - x: window bins.  Zero margins (usually the largest
+// single bin by far) go to a private counter per warp (h[NB + warp]) instead of one contended bin.
+template <int NT_, int QPT>
+__device__ __forceinline__ void hist_pass_win(Cx<NT_> &c, uint32_t ta, int base, uint32_t *h) {
+    const int zi = NB + c.warp;
+    if (c.lane == 0) h[zi] = 0u;
+    __syncwarp();
+    for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
+        if (q < c.TQ) {
+            const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+            const uint32_t k0 = __float_as_uint(__fsub_rn(E.x, x.x)), k1 = __float_as_uint(__fsub_rn(E.y, x.y));
+            const uint32_t k2 = __float_as_uint(__fsub_rn(E.z, x.z)), k3 = __float_as_uint(__fsub_rn(E.w, x.w));
+            atomicAdd(&h[k0 ? win_bin(k0, base) : zi], 1u);
+            atomicAdd(&h[k1 ? win_bin(k1, base) : zi], 1u);
+            atomicAdd(&h[k2 ? win_bin(k2, base) : zi], 1u);
+            atomicAdd(&h[k3 ? win_bin(k3, base) : zi], 1u);
+        }
+    });
+    __syncwarp();
+    if (c.lane == 0) { const uint32_t z = h[zi]; if (z) atomicAdd(&h[0], z); }
+    csync<NT_>();
+}
+// bracketed bins (refinement rounds: a coarse bin or heavy ties)
+template <int NT_, int QPT>
+__device__ __forceinline__ void hist_pass_range(Cx<NT_> &c, uint32_t ta, uint32_t lo, uint32_t hi, int sh, uint32_t *h) {
+    for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
+        if (q < c.TQ) {
+            const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+            const uint32_t k0 = __float_as_uint(__fsub_rn(E.x, x.x)), k1 = __float_as_uint(__fsub_rn(E.y, x.y));
+            const uint32_t k2 = __float_as_uint(__fsub_rn(E.z, x.z)), k3 = __float_as_uint(__fsub_rn(E.w, x.w));
+            if (k0 >= lo && k0 <= hi) atomicAdd(&h[(k0 - lo) >> sh], 1u);
+            if (k1 >= lo && k1 <= hi) atomicAdd(&h[(k1 - lo) >> sh], 1u);
+            if (k2 >= lo && k2 <= hi) atomicAdd(&h[(k2 - lo) >> sh], 1u);
+            if (k3 >= lo && k3 <= hi) atomicAdd(&h[(k3 - lo) >> sh], 1u);
+        }
+    });
+    csync<NT_>();
+}
+
+// agree, across the cluster, on the bin of the current histogram that holds rank r
+template <int NT_>
+__device__ __forceinline__ Located locate(Cx<NT_> &c, uint32_t r) {
+    constexpr int BPT = NB / HT;                // bins per scanning thread (the first HT threads scan)
+    constexpr int TPS = SUBB / BPT;             // threads per super bin
+    Misc *s = c.ms;
+    SelScratch *ss = sel(c);
+    uint32_t *h = ss->hist[c.hround & 1u];
+    if (c.tid < HT) {   // 64 super-bin sums of my histogram -> outbox
+        const uint4 hv = *reinterpret_cast<const uint4 *>(&h[BPT * c.tid]);
+        uint32_t v = hv.x + hv.y + hv.z + hv.w;
+#pragma unroll
+        for (int o = TPS / 2; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((c.tid & (TPS - 1)) == 0) outbox(c)[c.tid / TPS] = v;
+    }
+    if (c.tid == NT_ - 1) s->lcount = 0u;
+    const uint32_t (*box)[MBW] = exchange(c, NSB);
+    // every warp finds the super bin itself (64 sums x G CTAs)
+    int S = -1;
+    uint32_t preS = 0u;
+    {
+        uint32_t s0 = 0, s1 = 0;
+        for (int p = 0; p < c.G; p++) { const uint2 t = *reinterpret_cast<const uint2 *>(&box[p][2 * c.lane]); s0 += t.x; s1 += t.y; }
+        uint32_t inc = s0 + s1;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (c.lane >= o) inc += t;
+        }
+        const uint32_t ex = inc - (s0 + s1);
+        int mine = -1;
+        uint32_t mpre = 0u;
+        if (r >= ex && r < ex + s0) { mine = 2 * c.lane; mpre = ex; }
+        else if (r >= ex + s0 && r < ex + s0 + s1) { mine = 2 * c.lane + 1; mpre = ex + s0; }
+        const uint32_t bal = __ballot_sync(0xffffffffu, mine >= 0);
+        if (bal) {
+            const int src = __ffs(bal) - 1;
+            S = __shfl_sync(0xffffffffu, mine, src);
+            preS = __shfl_sync(0xffffffffu, mpre, src);
+        }
+    }
+    Located L;
+    L.bin = -1; L.pre = 0; L.cnt = 0;
+    c.hround++;
+    if (S < 0) return L;                               // uniform over the cluster
+    // the 32 fine bins of super bin S from every CTA: warp p fetches CTA p's
+    if (c.warp < c.G)
+        ss->fine[c.warp][c.lane] = (c.warp == c.rank) ? h[S * SUBB + c.lane] : ld_peer(peer_addr(&h[S * SUBB + c.lane], c.warp));
+    csync<NT_>();
+    {
+        uint32_t f = 0;
+        for (int p = 0; p < c.G; p++) f += ss->fine[p][c.lane];
+        uint32_t inc = f;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (c.lane >= o) inc += t;
+        }
+        const uint32_t ex = inc - f, rr = r - preS;
+        const bool hit = rr >= ex && rr < ex + f;
+        const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+        if (bal) {
+            const int src = __ffs(bal) - 1;
+            L.bin = S * SUBB + src;
+            L.pre = preS + __shfl_sync(0xffffffffu, ex, src);
+            L.cnt = __shfl_sync(0xffffffffu, f, src);
+        }
+    }
+    return L;
+}
+
+// exact selection of rank r among cnt keys in [lo, hi] held in CTA-local shared memory: histogram rounds
+template <int NT_>
+__device__ __forceinline__ uint32_t local_select_hist(Cx<NT_> &c, const uint32_t *keys, uint32_t cnt, uint32_t r,
+                                                      uint32_t lo, uint32_t hi) {
+    constexpr int BPT = NB / HT;
+    Misc *s = c.ms;
+    uint32_t *h = sel(c)->lhist;
+    for (int guard = 0; guard < 4; guard++) {
+        if (lo == hi) break;
+        int sh = 0;
+        while (((hi - lo) >> sh) >= (uint32_t)NB) sh++;
+        for (int i = c.tid; i < NB; i += NT_) h[i] = 0u;
+        csync<NT_>();
+        for (uint32_t i = c.tid; i < cnt; i += NT_) {
+            const uint32_t key = keys[i];
+            if (key >= lo && key <= hi) atomicAdd(&h[(key - lo) >> sh], 1u);
+        }
+        csync<NT_>();
+        uint32_t hv[BPT], mine = 0u;
+#pragma unroll
+        for (int e = 0; e < BPT; e++) { hv[e] = (c.tid < HT) ? h[BPT * c.tid + e] : 0u; mine += hv[e]; }
+        if (c.tid == 0) s->sel_bin = -1;
+        uint32_t total;
+        uint32_t ex = block_excl_scan_u32(c, mine, &total);
+#pragma unroll
+        for (int e = 0; e < BPT; e++) {
+            if (r >= ex && r < ex + hv[e]) { s->sel_bin = BPT * c.tid + e; s->sel_pre = ex; }
+            ex += hv[e];
+        }
+        csync<NT_>();
+        const int bin = s->sel_bin;
+        const uint32_t pre = s->sel_pre;
+        csync<NT_>();
+        if (bin < 0) { if (c.tid == 0) atomicExch(c.p->status, 300 + guard); return lo; }
+        r -= pre;
+        lo += (uint32_t)bin << sh;
+        const uint32_t top = lo + ((1u << sh) - 1u);
+        if (top < hi) hi = top;
+    }
+    return lo;
+}
+
+// the same by counting: candidate i has rank [lt, lt + eq) -- one CTA barrier, no histogram.
+// keys[cnt .. cnt+3] must hold 0xffffffff.
+template <int NT_>
+__device__ __forceinline__ uint32_t local_select_rank(Cx<NT_> &c, const uint32_t *keys, uint32_t cnt, uint32_t r) {
+    if ((uint32_t)c.tid < cnt) {
+        const uint32_t my = keys[c.tid];
+        uint32_t lt = 0u, eq = 0u;
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(keys);
+        for (uint32_t j = 0; j < cnt; j += 4) {
+            const uint4 g = k4[j >> 2];
+            lt += (g.x < my) + (g.y < my) + (g.z < my) + (g.w < my);
+            eq += (g.x == my) + (g.y == my) + (g.z == my) + (g.w == my);
+        }
+        if (lt <= r && r < lt + eq) c.ms->sel_key = my;
+    }
+    csync<NT_>();
+    return c.ms->sel_key;
+}
+
+// The value of rank k (0-based) among the margins E[i] - x[i] of the whole image; the plane is in the
+// TMEM slot at ta.  *zeros receives the exact number of zero margins when the selection saw them
+// (else 0xffffffff).
+template <int NT_, int QPT>
+__device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t k, float dmax_bound, uint32_t *zeros) {
+    SelScratch *ss = sel(c);
+    uint32_t e_top = (__float_as_uint(dmax_bound) >> 23) + 1u;
+    if (e_top > 254u) e_top = 254u;
+    const uint32_t lo_key = (e_top > (uint32_t)WIN_BINADES ? e_top - WIN_BINADES : 0u) << 23;
+    const int base = (int)(lo_key >> WIN_SH) - 2;
+    uint32_t lo = lo_key, hi = 0u, r = k;
+    int sh = 0;
+    bool window = true;
+    *zeros = 0xffffffffu;
+    for (int guard = 0; guard < 6; guard++) {
+        uint32_t *h = ss->hist[c.hround & 1u];          // zeroed since its last use
+        if (window) hist_pass_win<NT_, QPT>(c, ta, base, h);
+        else hist_pass_range<NT_, QPT>(c, ta, lo, hi, sh, h);
+        const Located L = locate(c, r);
+        // the histogram of the PREVIOUS round is no longer read by any peer (they all took part in this
+        // round's exchange after their fine-bin reads): clear it for the next round
+        {
+            uint4 *hz4 = reinterpret_cast<uint4 *>(ss->hist[c.hround & 1u]);
+            for (int i = c.tid; i < NBX / 4; i += NT_) hz4[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        if (L.bin < 0) {
+            if (c.tid == 0) atomicExch(c.p->status, 200 + guard);
+            csync<NT_>();
+            return 0.f;
+        }
+        uint32_t klo, khi;
+        if (window) win_range((uint32_t)L.bin, lo_key, klo, khi);
+        else {
+            klo = lo + ((uint32_t)L.bin << sh);
+            khi = min(hi, klo + ((1u << sh) - 1u));
+        }
+        if (window && L.bin == 0) *zeros = L.cnt;
+        r -= L.pre;
+        if (klo == khi) { csync<NT_>(); return __uint_as_float(klo); }
+        if (L.cnt <= (uint32_t)GCAP) {
+            // gather the candidates of the bin into every CTA, in rank order of the CTAs
+            for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
+                if (q >= c.TQ) return;
+                const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+                const uint32_t kk[4] = {__float_as_uint(__fsub_rn(E.x, x.x)), __float_as_uint(__fsub_rn(E.y, x.y)),
+                                        __float_as_uint(__fsub_rn(E.z, x.z)), __float_as_uint(__fsub_rn(E.w, x.w))};
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    if (kk[e] - klo <= khi - klo) {
+                        const uint32_t pos = atomicAdd(&c.ms->lcount, 1u);
+                        if (pos < (uint32_t)GCAP) ss->mylist[pos] = kk[e];
+                    }
+                }
+            });
+            const int fb = L.bin & (SUBB - 1);
+            const uint32_t mine = ss->fine[c.rank][fb];
+            uint32_t off = 0;
+            for (int p = 0; p < c.rank; p++) off += ss->fine[p][fb];
+            if (c.tid < 4) ss->gather[L.cnt + c.tid] = 0xffffffffu;
+            const uint32_t par = c.xround & 1u;
+            if (c.G > 1 && !(c.p->flags & V4_F_CLASSIC_XCHG)) {
+                if (c.tid == 0) mbar_expect_tx(&c.ms->xbar[par], L.cnt * 4u);
+                csync<NT_>();                            // my list is complete, the barrier is armed
+                for (uint32_t i = c.tid; i < (uint32_t)c.G * mine; i += NT_) {
+                    const uint32_t peer = i / mine, w = i - peer * mine;
+                    st_async_u32(peer_addr(&ss->gather[off + w], (int)peer), ss->mylist[w], peer_addr(&c.ms->xbar[par], (int)peer));
+                }
+                mbar_wait(&c.ms->xbar[par], (c.xround >> 1) & 1u, c.p, 403);
+                c.xround++;
+            } else if (c.G > 1) {
+                csync<NT_>();
+                for (uint32_t i = c.tid; i < (uint32_t)c.G * mine; i += NT_) {
+                    const uint32_t peer = i / mine, w = i - peer * mine;
+                    st_peer(peer_addr(&ss->gather[off + w], (int)peer), ss->mylist[w]);
+                }
+                cluster_sync_compute(c);
+            } else {
+                csync<NT_>();
+                for (uint32_t w = c.tid; w < mine; w += NT_) ss->gather[w] = ss->mylist[w];
+                csync<NT_>();
+            }
+            uint32_t key;
+            if (L.cnt <= (uint32_t)RCMAX && !(c.p->flags & V4_F_NO_RANKCOUNT)) key = local_select_rank(c, ss->gather, L.cnt, r);
+            else { key = local_select_hist(c, ss->gather, L.cnt, r, klo, khi); csync<NT_>(); }
+            return __uint_as_float(key);
+        }
+        // heavy ties or a coarse (out-of-window) bin: narrow the bracket and bin again
+        window = false;
+        lo = klo; hi = khi;
+        sh = 0;
+        while (((hi - lo) >> sh) >= (uint32_t)NB) sh++;
+        csync<NT_>();                                   // the cleared histogram before the next round's atomics
+    }
+    if (c.tid == 0) atomicExch(c.p->status, 299);
+    csync<NT_>();
+    return 0.f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// class planes: L2 scratch <-> tensor memory
+// ---------------------------------------------------------------------------------------------
+template <int NT_, int QPT> __device__ __forceinline__ uint32_t slot_addr(const Cx<NT_> &c, int slot) {
+    return c.tm + (uint32_t)(slot * slot_cols(QPT));
+}
+template <int NT_, int QPT>
+__device__ __forceinline__ void plane_load(Cx<NT_> &c, int plane, int slot) {
+    const float *src = c.planes + (size_t)plane * c.p->Npad + c.base;
+    const uint32_t ta = slot_addr<NT_, QPT>(c, slot);
+#pragma unroll
+    for (int k = 0; k < QPT; k++) {
+        const int q = k * NT_ + c.tid;
+        float4 v = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);     // quads beyond the tile
+        if (q < c.TQ) {
+            v = __ldcg(reinterpret_cast<const float4 *>(src + 4 * q));
+            if (4 * q + 3 >= c.n_t) {                   // the last quad of the image: padding pixels
+                if (4 * q + 1 >= c.n_t) v.y = -INFINITY;
+                if (4 * q + 2 >= c.n_t) v.z = -INFINITY;
+                v.w = -INFINITY;
+            }
+        }
+        tm_st4(ta + 4 * k, v);                          // warp-collective: every lane, every k
+    }
+    tm_wait_st();
+}
+template <int NT_, int QPT>
+__device__ __forceinline__ void plane_store(Cx<NT_> &c, int plane, int slot) {
+    float *dst = c.planes + (size_t)plane * c.p->Npad + c.base;
+    const uint32_t ta = slot_addr<NT_, QPT>(c, slot);
+    for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
+        if (q < c.TQ) __stcg(reinterpret_cast<float4 *>(dst + 4 * q), x);   // padding lanes of the last quad: never read as scores
+    });
+}
+// the TMEM slot that holds `plane` (loading it, and writing back the plane it replaces, if needed)
+template <int NT_, int QPT>
+__device__ __forceinline__ int plane_acquire(Cx<NT_> &c, int plane) {
+    constexpr int NS = n_slots(QPT);
+    int s;
+    if (c.res0 == plane) s = 0;
+    else if (NS > 1 && c.res1 == plane) s = 1;
+    else {
+        s = (NS > 1) ? (c.res0 < 0 ? 0 : (c.res1 < 0 ? 1 : (c.mru ^ 1))) : 0;
+        if (s == 0) {
+            if (c.res0 >= 0 && c.dirty0) plane_store<NT_, QPT>(c, c.res0, 0);
+            plane_load<NT_, QPT>(c, plane, 0);
+            c.res0 = plane;
+            c.dirty0 = false;
+        } else {
+            if (c.res1 >= 0 && c.dirty1) plane_store<NT_, QPT>(c, c.res1, 1);
+            plane_load<NT_, QPT>(c, plane, 1);
+            c.res1 = plane;
+            c.dirty1 = false;
+        }
+    }
+    c.mru = s;
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// labels (weaklabel.cpp:108-112 + deeplab.py:123)
+// ---------------------------------------------------------------------------------------------
+// Exact label of one pixel from the final scores of the present classes (vals[pl], float) and the
+// original scores of the absent ones, exactly as the reference forms them: suppressed (weaklabel.cpp:
+// 45-65), shifted in double, rounded to float (:110), first maximum (deeplab.py:123).
+template <typename V>
+static __device__ __forceinline__ int label_exact(const EStepParams &p, uint32_t mask, int b, int i, double shift, V &&val) {
+    const float *px = p.map + (long long)b * p.s0 + (long long)i * p.s2;
+    float m = FLT_MAX;
+    for (int k = 0; k < p.C; k++)
+        if ((mask >> k) & 1u) { const float t = px[k]; if (t < m) m = t; }
+    const float low = __fsub_rn(m, p.margin);
+    float best = -INFINITY;
+    int bi = 0, pp = 0;
+    for (int k = 0; k < p.C; k++) {
+        float v;
+        if ((mask >> k) & 1u) {
+            v = val(pp);
+            pp++;
+        } else {
+            v = px[k];
+            if (v > m) v = low;
+        }
+        const float fv = __double2float_rn(__dadd_rn((double)v, shift));
+        if (fv > best) { best = fv; bi = k; }
+    }
+    return bi;
+}
+
+template <int NT_, int QPT>
+__device__ __forceinline__ void write_labels(Cx<NT_> &c, double shift) {
+    const EStepParams &p = *c.p;
+    uint8_t *out = p.labels + (size_t)c.b * p.N + c.base;
+    const bool has_absent = c.P < p.C;
+    if (c.P == 1 && c.ms->plist[0] == 0) {
+        // background only: every absent class has a higher index and a score <= the background's
+        for (int i = c.tid; i < c.n_t; i += NT_) out[i] = 0;
+        return;
+    }
+    const bool have_abs = has_absent && c.P == 1;          // suppressed absent maximum was kept
+    // Two final scores a > b can round to the same float after the shift only if a - b is below the
+    // spacing of the floats around the shifted values: guard = 2^-22 * (|best| + |shift|) is at least
+    // twice that spacing.  Pixels inside the guard take the exact path.
+    const float ashift = __double2float_ru(fabs(shift));
+    const bool exact_all = (p.flags & V4_F_NO_FASTLABEL) != 0;
+    const uint32_t t0 = slot_addr<NT_, QPT>(c, 0), t1 = slot_addr<NT_, QPT>(c, 1 % n_slots(QPT));
+    const int r0 = c.res0, r1 = n_slots(QPT) > 1 ? c.res1 : -1;
+#pragma unroll 1
+    for (int k = 0; k < QPT; k++) {
+        // tcgen05.ld is warp-collective: both slots are read by every lane for every k
+        const float4 s0v = tm_ld4(t0 + 4 * k);
+        const float4 s1v = n_slots(QPT) > 1 ? tm_ld4(t1 + 4 * k) : s0v;
+        const int q = k * NT_ + c.tid;
+        if (q >= c.TQ) continue;
+        float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float near_[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // largest score strictly below best
+        float lowest[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+        int bi[4] = {0, 0, 0, 0};
+        for (int pl = 0; pl < c.P; pl++) {
+            float4 v;
+            if (r0 == pl) v = s0v;
+            else if (r1 == pl) v = s1v;
+            else v = __ldcg(reinterpret_cast<const float4 *>(c.planes + (size_t)pl * p.Npad + c.base + 4 * q));
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            const int cls = c.ms->plist[pl];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float t = vv[e];
+                if (t > best[e]) { near_[e] = best[e]; best[e] = t; bi[e] = cls; }
+                else if (t < best[e]) near_[e] = fmaxf(near_[e], t);
+                lowest[e] = fminf(lowest[e], t);
+            }
+        }
+        float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+        uchar4 ai = make_uchar4(0, 0, 0, 0);
+        if (have_abs) {
+            av = __ldcg(reinterpret_cast<const float4 *>(c.absmax + c.base + 4 * q));
+            ai = __ldcg(reinterpret_cast<const uchar4 *>(c.absidx + c.base + 4 * q));
+        }
+        const float ava[4] = {av.x, av.y, av.z, av.w};
+        const int aia[4] = {ai.x, ai.y, ai.z, ai.w};
+        const float s0a[4] = {s0v.x, s0v.y, s0v.z, s0v.w};
+        const float s1a[4] = {s1v.x, s1v.y, s1v.z, s1v.w};
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int i = 4 * q + e;
+            if (i >= c.n_t) continue;
+            const float guard = __fmul_ru(__fadd_ru(fabsf(best[e]), ashift), 2.4e-7f);       // > 2^-22
+            bool slow = exact_all || (__fsub_rn(best[e], near_[e]) <= guard);
+            if (have_abs) {
+                // one present class: the suppressed absent maximum is <= its score; it matters on a rounding tie
+                if (exact_all) slow = true;
+                else if (__fsub_rn(best[e], ava[e]) <= guard) {
+                    if (aia[e] == c.first_absent) {
+                        const float fa = __double2float_rn(__dadd_rn((double)ava[e], shift));
+                        const float fb = __double2float_rn(__dadd_rn((double)best[e], shift));
+                        if (fa >= fb) bi[e] = (fa > fb) ? aia[e] : min(aia[e], bi[e]);
+                    } else slow = true;
+                }
+            } else if (has_absent) {
+                // every suppressed absent score is <= the smallest ORIGINAL present score <= the smallest
+                // present final score: an absent class can reach the maximum only if all present classes
+                // round to the same float
+                if (__fsub_rn(best[e], lowest[e]) <= guard) slow = true;
+            }
+            if (slow) {
+                const float v0 = s0a[e], v1 = s1a[e];
+                bi[e] = label_exact(p, c.mask, c.b, c.base + i, shift, [&](int pp) {
+                    if (r0 == pp) return v0;
+                    if (r1 == pp) return v1;
+                    return __ldcg(c.planes + (size_t)pp * p.Npad + c.base + i);
+                });
+            }
+            out[i] = (uint8_t)bi[e];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------
+template <int NT_, int QPT>
+__global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __grid_constant__ EStepParams p) {
+    typedef Layout<NT_> LY;
+    constexpr int NW = NT_ / 32;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Cx<NT_> c;
+    c.p = &p;
+    c.tid = threadIdx.x;
+    c.lane = c.tid & 31;
+    c.warp = c.tid >> 5;
+    c.G = p.G;
+    c.rank = blockIdx.x % p.G;
+    const int slot = blockIdx.x / p.G;
+    unsigned char *staging;
+    {
+        unsigned char *q = smem_raw;
+        c.s_E = reinterpret_cast<float *>(q);
+        q += LY::A16((size_t)p.se_floats * 4);
+        c.mbox = reinterpret_cast<uint32_t (*)[MAXG][MBW]>(q);
+        q += LY::MBOX_BYTES;
+        c.ms = reinterpret_cast<Misc *>(q);
+        q += LY::A16(sizeof(Misc));
+        c.uni = q;
+        q += LY::uni_bytes();
+        c.outd = reinterpret_cast<Digest *>(q);
+        q += 2 * LY::A16(sizeof(Digest));
+        staging = q;
+    }
+    c.xround = 0;
+    c.hround = 0;
+    c.csyncs = 0;
+    c.base = c.rank * p.TS;
+    c.n_t = max(0, min(p.TS, p.N - c.base));
+    c.TQ = (c.n_t + 3) >> 2;
+    Misc *ms = c.ms;
+    if (c.tid == 0) {
+        for (int d = 0; d < NST; d++) mbar_init(&ms->full_bar[d], 1);
+        mbar_init(&ms->e0_bar, 1);
+        mbar_init(&ms->dig_bar, 1);
+        mbar_init(&ms->res_bar, 1);
+        for (int q = 0; q < 2; q++) {
+            mbar_init(&ms->cmd_bar[q], 1);
+            mbar_init(&ms->ready_bar[q], NPW);
+            mbar_init(&ms->xbar[q], 1);
+            mbar_init(&ms->sbar[q], p.G);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
+    if (c.warp == 0) tm_alloc512(&ms->tmem_base);
+    tm_fence_before();
+    hw_cluster_sync();                                  // every CTA's barriers exist before any remote arrival
+    tm_fence_after();
+    c.tm = ms->tmem_base + ((uint32_t)(c.warp & 3) << 21) + (uint32_t)((c.warp >> 2) * 4 * QPT);
+    if (c.tid >= NT_) {
+        producer_main<NT_>(p, ms, staging, slot, c.base, c.n_t);
+        hw_cluster_sync();
+        return;
+    }
+    const bool lead_thread = (c.rank == 0 && c.tid == 0);
+    const int L = p.L;
+
+    for (uint32_t seq = 0;; seq++) {
+        // claim the image of sequence number seq + 1 (and seq when seq == 0) for the cluster and
+        // hand it to the producers, which stream it while image seq is worked on
+        trc(c, 0, (seq << 8) | 1u);
+        if (c.rank == 0 && c.warp == 0) {
+            int img0 = 0, img1 = 0;
+            if (c.lane == 0) {
+                if (seq == 0) {
+                    const int t = atomicAdd(p.image_counter, 1);
+                    img0 = (t < p.B) ? (p.sched ? p.sched[t] : t) : p.B;
+                }
+                const int t = atomicAdd(p.image_counter, 1);
+                img1 = (t < p.B) ? (p.sched ? p.sched[t] : t) : p.B;
+            }
+            img0 = __shfl_sync(0xffffffffu, img0, 0);
+            img1 = __shfl_sync(0xffffffffu, img1, 0);
+            if (c.lane < c.G) {
+                if (seq == 0) st_peer(peer_addr(&ms->cmd_img[0], c.lane), (uint32_t)img0);
+                st_peer(peer_addr(&ms->cmd_img[(seq + 1) & 1u], c.lane), (uint32_t)img1);
+            }
+        }
+        cluster_sync_compute(c);
+        if (c.tid == 0) {
+            if (seq == 0) mbar_arrive(&ms->cmd_bar[0]);
+            mbar_arrive(&ms->cmd_bar[(seq + 1) & 1u]);
+        }
+        c.b = *reinterpret_cast<volatile int *>(&ms->cmd_img[seq & 1u]);
+        if (c.b >= p.B) break;
+        c.planes = p.planes + (size_t)(slot * 2 + (int)(seq & 1u)) * (size_t)(p.C + 2) * p.Npad;
+        c.absmax = c.planes + (size_t)p.C * p.Npad;
+        c.absidx = p.absent_idx + (size_t)(slot * 2 + (int)(seq & 1u)) * p.Npad;
+        unsigned long long *prof = p.prof ? p.prof + (size_t)c.b * 8 : nullptr;
+        if (prof && lead_thread) prof[0] = gtimer();
+        const ImageMeta *im = p.meta + c.b;
+        c.mask = im->mask;
+        c.P = im->P;
+        c.first_absent = im->first_absent;
+        c.res0 = c.res1 = -1;
+        c.dirty0 = c.dirty1 = false;
+        c.mru = 0;
+        if (c.tid < MAXC) {
+            ms->plist[c.tid] = im->plist[c.tid];
+            ms->zlb[c.tid] = 0u;
+        }
+        // 1. the planes of my tile are in the scratch (written by my producers together with E0, the
+        //    zero-margin counts, the tie count and the largest margin): E0 -> shared memory by bulk
+        //    copy, the first two planes -> tensor memory meanwhile
+        mbar_wait(&ms->ready_bar[seq & 1u], (seq >> 1) & 1u, &p, 404);
+        trc(c, 0, (seq << 8) | 3u);
+        trc(c, 1, (uint32_t)c.b);
+        const int n_t4 = (c.n_t + 3) & ~3;
+        if (c.tid == 0) {
+            const uint32_t bytes = (uint32_t)n_t4 * 4u;
+            if (bytes) {
+                asm volatile("fence.proxy.async;\n" ::: "memory");   // generic accesses to s_E (previous image) first
+                mbar_expect_tx(&ms->e0_bar, bytes);
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
+                for (uint32_t o = 0; o < bytes; o += 32768u)
+                    bulk_g2s(reinterpret_cast<unsigned char *>(c.s_E) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
+            } else {
+                mbar_arrive(&ms->e0_bar);
+            }
+        }
+        if (!(p.flags & V4_F_NO_RESIDENT)) {
+            plane_load<NT_, QPT>(c, 0, 0);
+            c.res0 = 0;
+            if (n_slots(QPT) > 1 && c.P > 1) { plane_load<NT_, QPT>(c, 1, 1); c.res1 = 1; c.mru = 1; }
+        }
+        {   // both histograms start every image cleared (in CTA 0 the incoming digests of the previous image lay there)
+            uint4 *h4 = reinterpret_cast<uint4 *>(sel(c)->hist);
+            for (int i = c.tid; i < 2 * NBX / 4; i += NT_) h4[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        mbar_wait(&ms->e0_bar, seq & 1u, &p, 405);
+        for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.s_E[i] = 0.f;      // padding pixels: E = 0
+        if (prof && lead_thread) prof[1] = gtimer();
+        csync<NT_>();
+
+        trc(c, 0, (seq << 8) | 4u);
+        // 2. one exchange: zero counts, largest margin, ties, tile totals (prediction for mean_max_0)
+        double tile_total;
+        double cs0;
+        const double cpre0 = chunk_prefix(c, &tile_total, &cs0);
+        if (c.tid < 6) {
+            uint32_t v = 0u;
+            for (int w = 0; w < NPW; w++) {
+                const uint32_t t = ms->pstat[seq & 1u][w][c.tid];
+                v = (c.tid == 4) ? max(v, t) : v + t;
+            }
+            outbox(c)[c.tid] = v;
+        }
+        if (c.tid == 32) {
+            const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
+            outbox(c)[6] = (uint32_t)tb;
+            outbox(c)[7] = (uint32_t)(tb >> 32);
+        }
+        float dmax_bound;
+        double before0 = 0.0;
+        uint32_t tie_bound = 0u;
+        {
+            const uint32_t (*box)[MBW] = exchange(c, 8);
+            uint32_t mx = 0u;
+            for (int q = 0; q < c.G; q++) {
+                mx = max(mx, box[q][4]);
+                tie_bound += box[q][5];
+                if (q < c.rank)
+                    before0 += __longlong_as_double((long long)((unsigned long long)box[q][6] | ((unsigned long long)box[q][7] << 32)));
+            }
+            dmax_bound = __uint_as_float(mx);
+            if (c.tid < EAGER_P && c.tid < c.P) {
+                uint32_t z = 0u;
+                for (int q = 0; q < c.G; q++) z += box[q][c.tid];
+                ms->zlb[c.tid] = z;
+            }
+        }
+        // 3. mean_max_0 (weaklabel.cpp:69-80): the digest of my tile's float running sum; CTA 0 walks its own
+        //    tile at once (no incoming state), the other tiles follow at the end of the image
+        build_big_digest<float, NT_>(c, cpre0, cs0, before0);
+        if (c.warp == 0) {
+            if (c.rank == 0) {
+                const BigDigest *big = &sums(c)->big;
+                const float s0 = walk_digest<float>(0.f, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.s_E,
+                                                    [&](int j) { return c.s_E[j]; });
+                if (c.lane == 0) ms->state0 = s0;
+            } else {
+                compact_digest(c, &c.outd[0]);
+            }
+        }
+        csync<NT_>();
+        if (prof && lead_thread) prof[2] = gtimer();
+
+        trc(c, 0, (seq << 8) | 6u);
+        // 4. iterations (weaklabel.cpp:82-101)
+        // The zero-margin lower bounds only pay when quotas leave slack (a class that keeps more pixels
+        // than its quota is skipped without a selection).  When the quotas of the label set add up to
+        // the whole image every step selects anyway: the per-fold exchange that maintains them is dropped.
+        bool track_zeros;
+        {
+            long long quota = 0;
+            for (int k = 0; k < c.P; k++) quota += (ms->plist[k] == 0) ? p.nth_bg : p.nth_fg;
+            track_zeros = quota < (long long)p.N - (p.N >> 6);
+        }
+        const uint8_t *ord = p.order + (size_t)c.b * p.num_iter * p.C;
+        uint32_t nsel = 0;
+        for (int j = 0; j < p.num_iter; j++) {
+            for (int t = 0; t < c.P; t++) {
+                const int plane = ord[j * p.C + t];
+                const int cls = ms->plist[plane];
+                const uint32_t k = (uint32_t)((cls == 0) ? p.nth_bg : p.nth_fg);      // weaklabel.cpp:88
+                float bias = 0.f;
+                if (k >= ms->zlb[plane]) {        // else: the rank falls among the zero margins, bias 0
+                    nsel++;
+                    trc(c, 0, (seq << 8) | 7u);
+                    trc(c, 2, ((uint32_t)j << 8) | (uint32_t)t);
+                    const int sl = plane_acquire<NT_, QPT>(c, plane);
+                    const uint32_t ta = slot_addr<NT_, QPT>(c, sl);
+                    uint32_t zeros;
+                    bias = select_margin<NT_, QPT>(c, ta, k, dmax_bound, &zeros);
+                    if (bias != 0.f) {
+                        // fold: x += bias (weaklabel.cpp:90-92), E = max(E, x) (:94-99)
+                        uint32_t gall = 0u, gnew = 0u, znew = 0u;
+                        for_each_quad<NT_, QPT>(c, ta, [&](int kq, int q, float4 x) {
+                            const float4 xn = make_float4(__fadd_rn(x.x, bias), __fadd_rn(x.y, bias), __fadd_rn(x.z, bias), __fadd_rn(x.w, bias));
+                            tm_st4(ta + 4 * kq, xn);                  // warp-collective (quads beyond the tile stay -inf)
+                            if (q >= c.TQ) return;
+                            float4 *Ep = reinterpret_cast<float4 *>(c.s_E + 4 * q);
+                            float4 E = *Ep;
+                            gall += (xn.x > E.x) + (xn.y > E.y) + (xn.z > E.z) + (xn.w > E.w);
+                            gnew += (xn.x > E.x && x.x < E.x) + (xn.y > E.y && x.y < E.y) + (xn.z > E.z && x.z < E.z) + (xn.w > E.w && x.w < E.w);
+                            znew += (xn.x >= E.x) + (xn.y >= E.y) + (xn.z >= E.z) + (xn.w >= E.w);
+                            E.x = fmaxf(E.x, xn.x); E.y = fmaxf(E.y, xn.y); E.z = fmaxf(E.z, xn.z); E.w = fmaxf(E.w, xn.w);
+                            *Ep = E;
+                        });
+                        tm_wait_st();
+                        if (sl) c.dirty1 = true; else c.dirty0 = true;
+                        if (track_zeros) {
+                            for (int o = 16; o; o >>= 1) {
+                                gall += __shfl_xor_sync(0xffffffffu, gall, o);
+                                gnew += __shfl_xor_sync(0xffffffffu, gnew, o);
+                                znew += __shfl_xor_sync(0xffffffffu, znew, o);
+                            }
+                            if (c.lane == 0) { ms->wred[c.warp][0] = gall; ms->wred[c.warp][1] = gnew; ms->wred[c.warp][2] = znew; }
+                            csync<NT_>();
+                            if (c.warp == 0) {
+                                uint32_t a0 = 0, a1 = 0, a2 = 0;
+                                if (c.lane < NW) { a0 = ms->wred[c.lane][0]; a1 = ms->wred[c.lane][1]; a2 = ms->wred[c.lane][2]; }
+                                for (int o = 16; o; o >>= 1) {
+                                    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+                                    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                                    a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+                                }
+                                if (c.lane == 0) { uint32_t *ob = outbox(c); ob[0] = a0; ob[1] = a1; ob[2] = a2; ob[3] = 0u; }
+                            }
+                            const uint32_t (*box)[MBW] = exchange(c, 4);
+                            uint32_t gall_s = 0u, gnew_s = 0u, znew_s = 0u;
+                            for (int q = 0; q < c.G; q++) { gall_s += box[q][0]; gnew_s += box[q][1]; znew_s += box[q][2]; }
+                            // Pixels that leave the zero-margin set of another class: those the folded class newly
+                            // exceeds (it was below the max there) plus, at most, the pixels that ever held an
+                            // exact tie at the max.  Folding creates a tie wherever the new score EQUALS the old max.
+                            const uint32_t loss = (p.flags & V4_F_LOOSE_ZEROS) ? gall_s : gnew_s + tie_bound;
+                            tie_bound += znew_s - gall_s;
+                            if (c.tid < c.P) {
+                                const uint32_t z = ms->zlb[c.tid];
+                                ms->zlb[c.tid] = (c.tid == plane) ? znew_s : (z > loss ? z - loss : 0u);
+                            }
+                        } else if (c.tid < c.P) {
+                            ms->zlb[c.tid] = 0u;                      // a valid lower bound without the exchange
+                        }
+                        dmax_bound = __fadd_rn(dmax_bound, bias);
+                    } else if (zeros != 0xffffffffu) {
+                        if (c.tid == 0) ms->zlb[plane] = zeros;       // exact count of zero margins
+                    }
+                    if (p.flags & V4_F_NO_RESIDENT) {                 // A/B: no residency across steps
+                        if (sl) { if (c.dirty1) plane_store<NT_, QPT>(c, plane, 1); c.res1 = -1; c.dirty1 = false; }
+                        else { if (c.dirty0) plane_store<NT_, QPT>(c, plane, 0); c.res0 = -1; c.dirty0 = false; }
+                    }
+                    csync<NT_>();
+                }
+                if (lead_thread) p.bias_out[((size_t)c.b * p.num_iter + j) * p.C + t] = bias;
+            }
+        }
+        if (prof && lead_thread) prof[3] = gtimer();
+
+        trc(c, 0, (seq << 8) | 8u);
+        // 5. mean_max_1 (weaklabel.cpp:102-106): digest of the double running sum of the final E; the
+        //    digests of both sums travel to CTA 0, whose first two warps walk them at the same time
+        double cs1;
+        const double cpre1 = chunk_prefix(c, &tile_total, &cs1);
+        if (c.tid == 32) {
+            const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
+            uint32_t *ob = outbox(c);
+            ob[0] = (uint32_t)tb; ob[1] = (uint32_t)(tb >> 32); ob[2] = 0u; ob[3] = 0u;
+        }
+        double before1 = 0.0;
+        {
+            const uint32_t (*box)[MBW] = exchange(c, 4);
+            for (int q = 0; q < c.rank; q++)
+                before1 += __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
+        }
+        // (after this exchange no CTA of the cluster is inside a selection any more: the selection
+        //  scratch of CTA 0, which the incoming digests alias, is free)
+        if (c.rank == 0 && c.tid == 0 && c.G > 1) mbar_expect_tx(&ms->dig_bar, (uint32_t)((c.G - 1) * 2 * sizeof(Digest)));
+        if (c.tid == 32) mbar_expect_tx(&ms->res_bar, 16u);
+        build_big_digest<double, NT_>(c, cpre1, cs1, before1);
+        if (c.rank != 0) {
+            if (c.warp == 0) {
+                compact_digest(c, &c.outd[1]);
+                asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // my digest writes -> visible to the copy engine
+                __syncwarp();
+                if (c.lane == 0) {
+                    bulk_s2peer(peer_addr(&sums(c)->inbound[c.rank][0], 0), &c.outd[0], (uint32_t)(2 * sizeof(Digest)), peer_addr(&ms->dig_bar, 0));
+                }
+            }
+        } else if (c.warp < 2) {
+            SumScratch *ss = sums(c);
+            if (c.warp == 0) {
+                // the double sum: my own tile out of my shared memory, then the digests of the peers
+                const BigDigest *big = &ss->big;
+                double s1 = walk_digest<double>(0.0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.s_E,
+                                                [&](int j) { return c.s_E[j]; });
+                if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 406);
+                for (int r = 1; r < c.G; r++) {
+                    const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
+                    if (n_t_r == 0) break;
+                    const Digest *d = &ss->inbound[r][1];
+                    const uint32_t remote = peer_addr(c.s_E, r);
+                    s1 = walk_digest<double>(s1, d->seg, d->nseg, d->cross, L, n_t_r, c.lane, nullptr,
+                                             [&](int j) { return __uint_as_float(ld_peer(remote + 4u * (uint32_t)j)); });
+                }
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(s1);
+                if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[1], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
+            } else {
+                // the float sum continues from the end of my own tile through the float digests of the peers
+                float s0 = ms->state0;
+                if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 407);
+                for (int r = 1; r < c.G; r++) {
+                    const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
+                    if (n_t_r == 0) break;
+                    const Digest *d = &ss->inbound[r][0];
+                    const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad + (size_t)r * p.TS;     // E0 plane of tile r (L2)
+                    s0 = walk_digest<float>(s0, d->seg, d->nseg, d->cross, L, n_t_r, c.lane, nullptr,
+                                            [&](int j) { return __ldcg(e0 + j); });
+                }
+                const unsigned long long bits = (unsigned long long)__float_as_uint(s0);
+                if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[0], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
+            }
+        }
+        mbar_wait(&ms->res_bar, seq & 1u, &p, 408);
+        const float sum0 = __uint_as_float((uint32_t)ms->sumres[0]);
+        const double sum1 = __longlong_as_double((long long)ms->sumres[1]);
+        const float mean0 = __fdiv_rn(sum0, (float)p.N);
+        const double mean1 = __ddiv_rn(sum1, (double)p.N);
+        const double shift = __dsub_rn((double)mean0, mean1);
+        if (lead_thread) {
+            p.mean0[c.b] = mean0;
+            p.mean1[c.b] = mean1;
+            p.shift[c.b] = shift;
+        }
+        if (prof && lead_thread) prof[4] = gtimer();
+        trc(c, 0, (seq << 8) | 9u);
+        if (p.labels) write_labels<NT_, QPT>(c, shift);
+        csync<NT_>();
+        if (prof && lead_thread) {
+            prof[5] = gtimer();
+            prof[6] = nsel;
+            prof[7] = (unsigned long long)c.P;
+        }
+    }
+    trc(c, 0, 0xEEEEu);
+    csync<NT_>();
+    if (c.warp == 0) tm_dealloc512(ms->tmem_base);
+    hw_cluster_sync();                                  // nobody leaves while a peer may still address its shared memory
+    trc(c, 0, 0xFFFFu);
+}
+
+template <int NT_, int QPT>
+static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t stream, int *max_clusters) {
+    const size_t smem = Layout<NT_>::total(p.se_floats);
+    cudaError_t e = cudaFuncSetAttribute(estep_v4_kernel<NT_, QPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(estep_v4_kernel<NT_, QPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((max_clusters ? 64 : n_clusters) * p.G));
+    cfg.blockDim = dim3(NT_ + NPW * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.G;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (max_clusters) {
+        int n = 0;
+        e = cudaOccupancyMaxActiveClusters(&n, estep_v4_kernel<NT_, QPT>, &cfg);
+        *max_clusters = (e == cudaSuccess) ? n : 0;
+        return e;
+    }
+    return cudaLaunchKernelEx(&cfg, estep_v4_kernel<NT_, QPT>, p);
+}
+
+static cudaError_t dispatch(const EStepParams &p, int qpt, int n_clusters, cudaStream_t stream, int *maxc) {
+    if (qpt == 1) return launch_t<V4_NT, 1>(p, n_clusters, stream, maxc);
+    if (qpt == 3) return launch_t<V4_NT, 3>(p, n_clusters, stream, maxc);
+    if (qpt == 9) return launch_t<V4_NT, 9>(p, n_clusters, stream, maxc);
+    if (qpt == 10) return launch_t<V4_NT, 10>(p, n_clusters, stream, maxc);
+    return cudaErrorInvalidValue;
+}
+
+size_t smem_bytes(int se_floats) { return Layout<V4_NT>::total(se_floats); }
+
+}  // namespace v4
+
+// Geometry of the v4 kernel for an image of N pixels with C classes and a given cluster size.
+static bool v4_try(int N, int C, int G, int tune_TS, V4Config *out) {
+    const int nt = V4_NT;
+    const int cap = 10 * nt * 4;
+    if (G < 1 || G > V4_MAXG) return false;
+    int TS = tune_TS ? tune_TS : (N + G - 1) / G;
+    TS = (TS + 3) / 4 * 4;
+    if (TS < 4) TS = 4;
+    if (TS > cap || (long long)TS * G < N) return false;
+    const int needq = (TS / 4 + nt - 1) / nt;
+    out->nt = nt;
+    out->qpt = needq <= 1 ? 1 : (needq <= 3 ? 3 : (needq <= 9 ? 9 : 10));
+    out->G = G;
+    out->TS = TS;
+    out->L = ((TS + nt - 1) / nt) | 1;                   // odd: conflict-free chunk walks
+    if (out->L > v4::DIG_L) return false;
+    out->se_floats = ((TS > nt * out->L ? TS : nt * out->L) + 3) / 4 * 4;
+    int cpx = (v4::STAGE_BYTES - 32) / (4 * C);
+    if (cpx < 1) return false;
+    out->cpx = cpx;
+    if (v4::smem_bytes(out->se_floats) > 232448) return false;
+    EStepParams p = {};
+    p.G = G;
+    p.se_floats = out->se_floats;
+    int maxc = 0;
+    if (v4::dispatch(p, out->qpt, 0, nullptr, &maxc) != cudaSuccess || maxc <= 0) {
+        cudaGetLastError();
+        return false;
+    }
+    out->max_clusters = maxc;
+    return true;
+}
+
+// tune_G = 0: automatic -- the smallest power-of-two cluster that holds the image (two planes in tensor
+// memory need at most 9 quads per thread); large batches of large images take clusters of 9 (non-portable
+// size): on B200 as many of them are co-resident as clusters of 8 (15), so 135 instead of 120 SMs work.
+bool v4_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V4Config *out) {
+    if (tune_G) return v4_try(N, C, tune_G, tune_TS, out);
+    const int cap = 9 * V4_NT * 4;
+    int G = 1;
+    while (G < 8 && (N + G - 1) / G > cap) G *= 2;
+    while (G < 8 && (long long)B * G * 2 <= sms && N / (2 * G) >= 4096) G *= 2;
+    bool ok = v4_try(N, C, G, tune_TS, out);
+    if (G == 8 && tune_TS == 0) {
+        V4Config alt;
+        if (v4_try(N, C, 9, 0, &alt) && (!ok || (alt.max_clusters >= out->max_clusters && B >= alt.max_clusters) || alt.qpt < out->qpt)) { *out = alt; ok = true; }
+    }
+    return ok;
+}
+
+cudaError_t launch_estep_v4(const EStepParams &p, const V4Config &cfg, int n_clusters, cudaStream_t stream) {
+    return v4::dispatch(p, cfg.qpt, n_clusters, stream, nullptr);
+}
+
+}  // namespace wl

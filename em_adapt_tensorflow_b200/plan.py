@@ -64,8 +64,8 @@ class EStepPlan:
         return self
 
     def set_path(self, path):
-        """0 auto, 1 generic kernel, 4 ("fast") warp-specialised on-chip path, 2 ("fast2") / 3 ("fast1") its predecessors (labels() fails if a forced path does not apply)."""
-        _lib.check(self._L.weaklabel_plan_set_path(self.handle, {"auto": 0, "generic": 1, "fast2": 2, "fast1": 3, "fast": 4}.get(path, path)))
+        """0 auto, 1 generic kernel, 5 ("fast") the on-chip path (estep_v4.cu), 4 ("fast3") / 2 ("fast2") / 3 ("fast1") its predecessors (labels() fails if a forced path does not apply)."""
+        _lib.check(self._L.weaklabel_plan_set_path(self.handle, {"auto": 0, "generic": 1, "fast2": 2, "fast1": 3, "fast3": 4, "fast": 5}.get(path, path)))
         return self
 
     def set_threads(self, threads_per_cta):
@@ -82,7 +82,7 @@ class EStepPlan:
 
     @property
     def last_path(self):
-        return {0: None, 1: "generic", 2: "fast2", 3: "fast1", 4: "fast"}[self._L.weaklabel_plan_last_path(self.handle)]
+        return {0: None, 1: "generic", 2: "fast2", 3: "fast1", 4: "fast3", 5: "fast"}[self._L.weaklabel_plan_last_path(self.handle)]
 
     def prepare(self, present, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2,
                 rng=None):
