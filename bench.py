@@ -222,8 +222,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--parity-images", type=int, default=8)
     ap.add_argument("--tune", default="", help="cluster,tile,clusters for weaklabel_plan_tune")
-    ap.add_argument("--threads", type=int, default=0, help="threads per CTA of the fast kernel (0 auto, 512, 1024)")
-    ap.add_argument("--path", default="auto", help="auto | generic | fast | fast2 | fast1")
+    ap.add_argument("--path", default="auto", help="auto | generic | fast")
     ap.add_argument("--phase-profile", default="", help="write per-image phase stamps of one extra run to this .npy")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -275,8 +274,6 @@ def main():
     plan = wl.EStepPlan(B, H, W, C, device=local_rank)
     if args.tune:
         plan.tune(*[int(x) for x in args.tune.split(",")])
-    if args.threads:
-        plan.set_threads(args.threads)
     if args.path != "auto":
         plan.set_path(args.path)
     stream = wl.positioned_stream(present_all, PARAMS["num_iter"], lo)
@@ -374,7 +371,7 @@ def main():
                                 l2="inputs 5.66 GB per GPU >> 126 MB L2 (no flush needed)",
                                 parallelism="image-sharded x%d, no collective" % world),
                     roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                                  traffic=ncu_traffic(), kernel={"fast": "estep_v4_kernel", "fast3": "estep_v3_kernel", "fast2": "estep_v2_kernel", "fast1": "estep_fast_kernel", "generic": "estep_cluster_kernel"}.get(plan.last_path, "?"),
+                                  traffic=ncu_traffic(), kernel={"fast": "estep_onchip_kernel", "generic": "estep_cluster_kernel"}.get(plan.last_path, "?"),
                                   alg_bytes_per_pixel=ALG_BYTES_PER_PIXEL, kernel_ms=k_ms, peak_source=peak_src),
                     cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clocks, parity=parity)
         print(json.dumps(line), flush=True)

@@ -66,7 +66,6 @@ def load():
     L.weaklabel_plan_set_path.argtypes = [C.c_void_p, C.c_int]
     L.weaklabel_plan_last_path.argtypes = [C.c_void_p]
     L.weaklabel_plan_launches.argtypes = [C.c_void_p]
-    L.weaklabel_plan_set_threads.argtypes = [C.c_void_p, C.c_int]
     L.weaklabel_plan_profile.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     L.weaklabel_plan_launches.restype = C.c_longlong
     L.e_step_labels_device.argtypes = [C.c_void_p, _i32p, _i32p, _i32p, C.c_bool, C.c_int, C.c_float,
@@ -89,5 +88,5 @@ EXPORTS = ["e_step", "e_step_labels_device", "weaklabel_last_error", "weaklabel_
            "weaklabel_plan_prepare", "weaklabel_estep_labels_device",
            "weaklabel_estep_finalize_map_device", "weaklabel_plan_probes", "weaklabel_plan_tune",
            "weaklabel_plan_launches", "weaklabel_plan_set_path", "weaklabel_plan_last_path",
-           "weaklabel_plan_set_threads", "weaklabel_plan_profile",
+           "weaklabel_plan_profile",
            "weaklabel_softmax_ce_device"]

@@ -158,7 +158,7 @@ extern "C" WL_API int weaklabel_draw_order_host(const unsigned char *present, in
 }
 
 // ---------------------------------------------------------------------------------------------
-// debugging aid (WEAKLABEL_V3_TRAIL=1): progress words of every CTA of the warp-specialised kernel
+// debugging aid (WEAKLABEL_TRAIL=1): progress words of every CTA of the warp-specialised kernel
 // in mapped host memory, printed at process exit -- they survive a device-side exception
 // ---------------------------------------------------------------------------------------------
 static unsigned int *g_trail = nullptr;
@@ -178,7 +178,7 @@ static volatile unsigned int *debug_trail() {
     static bool tried = false;
     if (!tried) {
         tried = true;
-        if (getenv("WEAKLABEL_V3_TRAIL")) {
+        if (getenv("WEAKLABEL_TRAIL")) {
             void *h = nullptr;
             if (cudaHostAlloc(&h, 160 * 32 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
                 memset(h, 0, 160 * 32 * sizeof(unsigned int));
@@ -198,13 +198,10 @@ static volatile unsigned int *debug_trail() {
 struct weaklabel_plan {
     int B, H, W, C, N, device, sms;
     int G, TS, ntiles, L, Npad, slots, sub_px;      // generic kernel (estep_kernel.cu)
-    int fG, fTS, fL, fslots;                        // on-chip fast path (estep_fast.cu); fG == 0: unavailable
-    int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 fast (v2), 3 first-generation fast
-    int tune_nt;                                    // v2 threads per CTA (0 auto, 512, 1024)
-    V2Config v2; bool v2_ok; int v2_slots;          // second-generation kernel (estep_v2.cu)
-    V3Config v3; bool v3_ok; int v3_slots;          // third-generation kernel (estep_v3.cu), tune_path 4
-    V4Config v4; bool v4_ok; int v4_slots;          // fourth-generation kernel (estep_v4.cu), tune_path 5 (the default)
-    unsigned long long *d_prof; bool prof_on;       // [B][8] phase time stamps
+    int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 on-chip
+    OnchipConfig oc; bool oc_ok; int oc_slots;      // on-chip kernel (estep_onchip.cu)
+    int env_prefetch, env_flags;                    // WEAKLABEL_PREFETCH / WEAKLABEL_FLAGS, read once at creation
+    unsigned long long *d_prof; bool prof_on;       // [B][32] phase time stamps
     bool geometry_ok;
     int scratch_slots;
     int *d_sched;
@@ -240,7 +237,11 @@ static int plan_geometry(weaklabel_plan *pl) {
     if (pl->geometry_ok) return WEAKLABEL_OK;
     const int N = pl->N;
     int G = pl->tune_G;
-    if (G == 9) G = 8;                                  // clusters of 9 exist for the warp-specialised kernel only
+    if (G > 0 && G != 16) {                             // the generic kernel takes power-of-two clusters: round down
+        int g2 = 1;                                     // (sizes 3, 5, 6, 7, 9 exist for the on-chip kernel only)
+        while (g2 * 2 <= G && g2 < 8) g2 *= 2;
+        G = g2;
+    }
     if (G == 0) {
         G = 1;
         while (G < 8 && (N + G - 1) / G > TS_MAX) G *= 2;
@@ -272,71 +273,18 @@ static int plan_geometry(weaklabel_plan *pl) {
     if (slots > pl->B) slots = pl->B;
     if (slots < 1) slots = 1;
     pl->slots = slots;
-    // fast path: one tile of at most FAST_PPT_MAX*NT pixels per CTA, so the cluster must be large
-    // enough to hold the image; small batches take larger clusters to fill the device
-    pl->fG = 0;
-    {
-        const int cap = FAST_PPT_MAX * NT;
-        int fG = pl->tune_G == 9 ? 8 : pl->tune_G;
-        if (fG == 0) {
-            fG = 1;
-            while (fG < MAX_CLUSTER && (N + fG - 1) / fG > cap) fG *= 2;
-            while (fG < 8 && (long long)pl->B * fG * 2 <= pl->sms && N / (2 * fG) >= 4096) fG *= 2;
-        }
-        int fTS = pl->tune_TS ? pl->tune_TS : (N + fG - 1) / fG;
-        fTS = (fTS + 3) / 4 * 4;
-        if (fTS < 4) fTS = 4;
-        if (fTS <= cap && (long long)fTS * fG >= N && fast_ppt_for(fTS) > 0) {
-            int fmax = estep_fast_max_clusters(fG, fTS);
-            if (fmax > 0) {
-                int fs = pl->tune_slots ? pl->tune_slots : fmax;
-                if (fs > fmax) fs = fmax;
-                if (fs > pl->B) fs = pl->B;
-                if (fs < 1) fs = 1;
-                pl->fG = fG; pl->fTS = fTS; pl->fslots = fs;
-                pl->fL = (fTS + NT - 1) / NT;
-                if (pl->fL % 2 == 0) pl->fL++;
-            } else {
-                cudaGetLastError();
-            }
-        }
-    }
-    pl->v2_ok = v2_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, pl->tune_nt, &pl->v2);
-    if (pl->v2_ok) {
-        int vs = pl->tune_slots ? pl->tune_slots : pl->v2.max_clusters;
-        if (vs > pl->v2.max_clusters) vs = pl->v2.max_clusters;
+    pl->oc_ok = onchip_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, &pl->oc);
+    if (pl->oc_ok) {
+        int vs = pl->tune_slots ? pl->tune_slots : pl->oc.max_clusters;
+        if (vs > pl->oc.max_clusters) vs = pl->oc.max_clusters;
         if (vs > pl->B) vs = pl->B;
         if (vs < 1) vs = 1;
-        pl->v2_slots = vs;
+        pl->oc_slots = vs;
     }
-    pl->v3_ok = (pl->tune_nt == 0) && v3_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, &pl->v3);
-    if (pl->v3_ok) {
-        int vs = pl->tune_slots ? pl->tune_slots : pl->v3.max_clusters;
-        if (vs > pl->v3.max_clusters) vs = pl->v3.max_clusters;
-        if (vs > pl->B) vs = pl->B;
-        if (vs < 1) vs = 1;
-        pl->v3_slots = vs;
-    }
-    pl->v4_ok = (pl->tune_nt == 0) && v4_configure(N, pl->C, pl->B, pl->sms, pl->tune_G, pl->tune_TS, &pl->v4);
-    if (pl->v4_ok) {
-        int vs = pl->tune_slots ? pl->tune_slots : pl->v4.max_clusters;
-        if (vs > pl->v4.max_clusters) vs = pl->v4.max_clusters;
-        if (vs > pl->B) vs = pl->B;
-        if (vs < 1) vs = 1;
-        pl->v4_slots = vs;
-    }
-    if (pl->tune_path == 5 && !pl->v4_ok)
-        return fail(WEAKLABEL_ERR_ARG, "the fourth-generation fast path cannot hold %d pixels with this cluster/tile tuning", N);
-    if (pl->tune_path == 2 && !pl->v2_ok)
-        return fail(WEAKLABEL_ERR_ARG, "the fast path cannot hold %d pixels with this cluster/tile tuning", N);
-    if (pl->tune_path == 4 && !pl->v3_ok)
-        return fail(WEAKLABEL_ERR_ARG, "the warp-specialised fast path cannot hold %d pixels with this cluster/tile tuning", N);
-    if (pl->tune_path == 3 && pl->fG == 0)
-        return fail(WEAKLABEL_ERR_ARG, "the first-generation fast path cannot hold %d pixels with this cluster/tile tuning", N);
-    int ss = pl->fG && pl->fslots > slots ? pl->fslots : slots;
-    if (pl->v2_ok && pl->v2_slots > ss) ss = pl->v2_slots;
-    if (pl->v3_ok && 2 * pl->v3_slots > ss) ss = 2 * pl->v3_slots;      // two plane sets per resident cluster
-    if (pl->v4_ok && 2 * pl->v4_slots > ss) ss = 2 * pl->v4_slots;
+    if (pl->tune_path == 2 && !pl->oc_ok)
+        return fail(WEAKLABEL_ERR_ARG, "the on-chip kernel cannot hold %d pixels with this cluster/tile tuning", N);
+    int ss = slots;
+    if (pl->oc_ok && 2 * pl->oc_slots > ss) ss = 2 * pl->oc_slots;      // two plane sets per resident cluster
     pl->scratch_slots = ss;
     CUDA_TRY(cudaMalloc(&pl->d_planes, (size_t)ss * (pl->C + 2) * pl->Npad * sizeof(float)));
     CUDA_TRY(cudaMalloc(&pl->d_absidx, (size_t)ss * pl->Npad));
@@ -363,6 +311,12 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
                     "this library is built for sm_100a", device, prop.name, prop.major, prop.minor);
     weaklabel_plan *pl = new weaklabel_plan();
     pl->prepared = false;
+    {
+        const char *pf = getenv("WEAKLABEL_PREFETCH");      // tuning knob: chunks of L2 prefetch distance
+        pl->env_prefetch = pf ? atoi(pf) : OC_PF_AHEAD;
+        const char *fl = getenv("WEAKLABEL_FLAGS");         // A/B switches (estep_kernel.cuh: OC_F_*)
+        pl->env_flags = fl ? atoi(fl) : 0;
+    }
     pl->launches = 0;
     pl->last_stream = nullptr;
     pl->B = B; pl->H = H; pl->W = W; pl->C = C; pl->N = H * W;
@@ -374,8 +328,8 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean1, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_shift, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_sched, (size_t)B * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc(&pl->d_prof, (size_t)B * 8 * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemset(pl->d_prof, 0, (size_t)B * 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_prof, (size_t)B * 32 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(pl->d_prof, 0, (size_t)B * 32 * sizeof(unsigned long long));
     if (e != cudaSuccess) {
         weaklabel_plan_destroy(pl);
         return fail(WEAKLABEL_ERR_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
@@ -407,27 +361,17 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
 extern "C" WL_API long long weaklabel_plan_launches(const weaklabel_plan *pl) { return pl ? pl->launches : 0; }
 
 extern "C" WL_API int weaklabel_plan_set_path(weaklabel_plan *pl, int path) {
-    if (!pl || path < 0 || path > 5) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic), 2..4 (earlier generations of the fast kernel) or 5 (fast)");
+    if (!pl || path < 0 || path > 2) return fail(WEAKLABEL_ERR_ARG, "path must be 0 (auto), 1 (generic) or 2 (on-chip)");
     pl->tune_path = path;
     return WEAKLABEL_OK;
 }
 extern "C" WL_API int weaklabel_plan_last_path(const weaklabel_plan *pl) { return pl ? pl->last_path : 0; }
 
-extern "C" WL_API int weaklabel_plan_set_threads(weaklabel_plan *pl, int threads_per_cta) {
-    if (!pl || (threads_per_cta != 0 && threads_per_cta != 512 && threads_per_cta != 1024))
-        return fail(WEAKLABEL_ERR_ARG, "threads per CTA must be 0 (auto), 512 or 1024");
-    CUDA_TRY(cudaSetDevice(pl->device));
-    if (pl->last_stream || pl->geometry_ok) CUDA_TRY(cudaDeviceSynchronize());
-    plan_free_geometry(pl);
-    pl->tune_nt = threads_per_cta;
-    return WEAKLABEL_OK;
-}
-
 extern "C" WL_API int weaklabel_plan_profile(weaklabel_plan *pl, int enable, unsigned long long *out) {
     if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
     CUDA_TRY(cudaSetDevice(pl->device));
     if (pl->last_stream) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
-    if (out) CUDA_TRY(cudaMemcpy(out, pl->d_prof, (size_t)pl->B * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (out) CUDA_TRY(cudaMemcpy(out, pl->d_prof, (size_t)pl->B * 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     pl->prof_on = enable != 0;
     return WEAKLABEL_OK;
 }
@@ -531,46 +475,20 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.planes = pl->d_planes; p.absent_idx = pl->d_absidx; p.ctl = pl->d_ctl;
     // the on-chip fast path covers suppress_others with a margin >= 0 on contiguous pixels
     // (weaklabel.cpp:45-65 then guarantees that no absent class exceeds a present one)
-    const bool cond_ok = pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
-    const bool v2_ok = pl->v2_ok && cond_ok;
-    const bool fast1_ok = pl->fG > 0 && cond_ok;
-    const bool v3_ok = pl->v3_ok && cond_ok;
-    const bool v4_ok = pl->v4_ok && cond_ok;
-    if (pl->tune_path == 5 && !v4_ok)
-        return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
+    const bool oc_ok = pl->oc_ok && pl->suppress && pl->margin >= 0.f && pixel_stride == pl->C;
+    if (pl->tune_path == 2 && !oc_ok)
+        return fail(WEAKLABEL_ERR_ARG, "on-chip path forced but not applicable (needs suppress_others, margin >= 0, "
                     "contiguous pixels)");
-    if (pl->tune_path == 4 && !v3_ok)
-        return fail(WEAKLABEL_ERR_ARG, "warp-specialised fast path forced but not applicable (needs suppress_others, "
-                    "margin >= 0, contiguous pixels)");
-    if (pl->tune_path == 2 && !v2_ok)
-        return fail(WEAKLABEL_ERR_ARG, "fast path forced but not applicable (needs suppress_others, margin >= 0, "
-                    "contiguous pixels)");
-    if (pl->tune_path == 3 && !fast1_ok)
-        return fail(WEAKLABEL_ERR_ARG, "first-generation fast path forced but not applicable");
-    const int path = pl->tune_path ? pl->tune_path : (v4_ok ? 5 : (v3_ok ? 4 : (v2_ok ? 2 : 1)));
+    const int path = pl->tune_path ? pl->tune_path : (oc_ok ? 2 : 1);
     int slots_used = pl->slots;
     p.Npad = pl->Npad; p.sub_px = pl->sub_px;
     if (path == 2) {
-        p.TS = pl->v2.TS; p.ntiles = pl->v2.G; p.L = pl->v2.L; p.G = pl->v2.G; p.sub_px = pl->v2.cpx;
-        slots_used = pl->v2_slots;
-    } else if (path == 4) {
-        p.TS = pl->v3.TS; p.ntiles = pl->v3.G; p.L = pl->v3.L; p.G = pl->v3.G; p.sub_px = pl->v3.cpx;
-        slots_used = pl->v3_slots;
-        const char *pf = getenv("WEAKLABEL_V3_PREFETCH");          // tuning knob: chunks of L2 prefetch distance
-        p.pf_ahead = pf ? atoi(pf) : V3_PF_AHEAD;
+        p.TS = pl->oc.TS; p.ntiles = pl->oc.G; p.L = pl->oc.L; p.G = pl->oc.G; p.sub_px = pl->oc.cpx;
+        p.se_floats = pl->oc.se_floats;
+        slots_used = pl->oc_slots;
+        p.pf_ahead = pl->env_prefetch;
+        p.flags = pl->env_flags;
         p.trail = debug_trail();
-    } else if (path == 5) {
-        p.TS = pl->v4.TS; p.ntiles = pl->v4.G; p.L = pl->v4.L; p.G = pl->v4.G; p.sub_px = pl->v4.cpx;
-        p.se_floats = pl->v4.se_floats;
-        slots_used = pl->v4_slots;
-        const char *pf = getenv("WEAKLABEL_V3_PREFETCH");          // tuning knob: chunks of L2 prefetch distance
-        p.pf_ahead = pf ? atoi(pf) : V3_PF_AHEAD;
-        const char *fl = getenv("WEAKLABEL_V4_FLAGS");             // A/B switches (estep_kernel.cuh: V4_F_*)
-        p.flags = fl ? atoi(fl) : 0;
-        p.trail = debug_trail();
-    } else if (path == 3) {
-        p.TS = pl->fTS; p.ntiles = (pl->N + pl->fTS - 1) / pl->fTS; p.L = pl->fL; p.G = pl->fG;
-        slots_used = pl->fslots;
     } else {
         p.TS = pl->TS; p.ntiles = pl->ntiles; p.L = pl->L; p.G = pl->G;
     }
@@ -580,12 +498,12 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
     p.prof = pl->prof_on ? pl->d_prof : nullptr;
     CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
-    if (path != 2 && path != 4 && path != 5) CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
-    if (path == 5) CUDA_TRY(launch_estep_v4(p, pl->v4, slots_used, st));
-    else if (path == 4) CUDA_TRY(launch_estep_v3(p, pl->v3, slots_used, st));
-    else if (path == 2) CUDA_TRY(launch_estep_v2(p, pl->v2, slots_used, st));
-    else if (path == 3) CUDA_TRY(launch_estep_fast(p, slots_used, st));
-    else CUDA_TRY(launch_estep(p, slots_used, st));
+    if (path == 2) {
+        CUDA_TRY(launch_estep_onchip(p, pl->oc, slots_used, st));
+    } else {
+        CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
+        CUDA_TRY(launch_estep(p, slots_used, st));
+    }
     pl->last_path = path;
     pl->launches += 1;
     pl->last_stream = st;

@@ -48,7 +48,7 @@ struct EStepParams {
     SlotCtl *ctl;             // [slots]
     int Npad, TS, ntiles, L, G;
     int sub_px;               // pixels per streaming sub-tile
-    int pf_ahead;             // v3: chunks prefetched into the L2 ahead of the staging ring
+    int pf_ahead;             // chunks prefetched into the L2 ahead of the staging ring
     int *image_counter;
     const int *sched;         // [B] order in which images are claimed (largest label sets first), or NULL
     int *status;              // device-side error flag (0 = ok)
@@ -59,64 +59,34 @@ struct EStepParams {
     double *mean1;            // [B]
     double *shift;            // [B]  (double)mean0 - mean1
     unsigned long long *prof; // [B][8] phase time stamps (globaltimer ns) or NULL
-    volatile unsigned int *trail;  // v3 debugging: [CTA][16] progress words in mapped host memory, or NULL
-    // v4
+    volatile unsigned int *trail;  // debugging: [CTA][16] progress words in mapped host memory, or NULL
+    // on-chip kernel
     int se_floats;            // floats of the running-max tile in shared memory (>= TS and >= NT * L)
-    int flags;                // V4_F_* switches (A/B runs and bisection; 0 = everything on)
+    int flags;                // OC_F_* switches (A/B runs and bisection; 0 = everything on)
     unsigned long long *prof2; // [B][32] fine-grained phase accumulators (ns) or NULL
 };
 
-// v4 switches: a set bit turns the named optimisation OFF (falls back to the simpler code path)
-constexpr int V4_F_NO_RANKCOUNT = 1;      // local selection always by histogram rounds
-constexpr int V4_F_NO_RESIDENT = 2;       // evict the class plane after every step (no TMEM residency across steps)
-constexpr int V4_F_NO_FASTLABEL = 4;      // every pixel takes the exact (double) label path
-constexpr int V4_F_LOOSE_ZEROS = 8;       // first-generation zero-count bound (counts every pixel above the old max)
-constexpr int V4_F_NO_DIGEST = 16;        // sums: the walker fetches every segment from its owner (no pushed digests)
-constexpr int V4_F_CLASSIC_XCHG = 32;     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
+// switches of the on-chip kernel: a set bit turns the named optimisation OFF (falls back to the simpler code path)
+constexpr int OC_F_NO_RANKCOUNT = 1;      // local selection always by histogram rounds
+constexpr int OC_F_NO_RESIDENT = 2;       // evict the class plane after every step (no TMEM residency across steps)
+constexpr int OC_F_NO_FASTLABEL = 4;      // every pixel takes the exact (double) label path
+constexpr int OC_F_LOOSE_ZEROS = 8;       // first-generation zero-count bound (counts every pixel above the old max)
+constexpr int OC_F_NO_DIGEST = 16;        // sums: the walker fetches every segment from its owner (no pushed digests)
+constexpr int OC_F_CLASSIC_XCHG = 32;     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
 
 size_t estep_smem_bytes();
 cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream);
 int estep_max_clusters(int G);
 
-// on-chip fast path (estep_fast.cu): one tile of at most FAST_PPT_MAX * NT pixels per CTA
-constexpr int FAST_PPT_SMALL = 4;
-constexpr int FAST_PPT_MAX = 33;
-int fast_ppt_for(int tile_pixels);                     // 0 when the tile does not fit
-cudaError_t launch_estep_fast(const EStepParams &p, int n_clusters, cudaStream_t stream);
-int estep_fast_max_clusters(int G, int tile_pixels);
-
-// second-generation kernel of the common configuration (estep_v2.cu)
-constexpr int V2_PPT_SMALL = 4;
-constexpr int V2_PPT_MAX = 33;
-struct V2Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
-bool v2_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, int tune_nt, V2Config *out);
-cudaError_t launch_estep_v2(const EStepParams &p, const V2Config &cfg, int n_clusters, cudaStream_t stream);
-
-// third-generation kernel (estep_v3.cu): warp-specialised, producers stream image t+1 while the
-// compute threads work on image t; the scratch holds TWO plane sets per resident cluster
-constexpr int V3_NT = 896;            // compute threads per CTA
-constexpr int V3_NPW = 4;             // producer warps per CTA
-constexpr int V3_NST = 8;             // stages of the staging ring: a multiple of V3_NPW, so that a stage is
-                                      // always filled for, and drained by, the same warp (which then waits for
-                                      // its phases in order -- a warp must never wait one phase ahead)
-constexpr int V3_STAGE_BYTES = 7168;
-constexpr int V3_PF_AHEAD = 16;       // chunks prefetched into the L2 ahead of the ring
-constexpr int V3_MAXG = 9;
-constexpr int V3_PPT_SMALL = 4;
-constexpr int V3_PPT_MID = 12;
-constexpr int V3_PPT_BIG = 33;
-constexpr int V3_PPT_MAX = 37;
-struct V3Config { int nt, ppt, G, TS, L, cpx, max_clusters; };
-bool v3_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V3Config *out);
-cudaError_t launch_estep_v3(const EStepParams &p, const V3Config &cfg, int n_clusters, cudaStream_t stream);
-
-// fourth-generation kernel (estep_v4.cu): quad (float4) pixel ownership, two class planes resident in
-// tensor memory, branch-free histogram pass, st.async exchanges, digest-based order-exact sums
-constexpr int V4_NT = 896;
-constexpr int V4_MAXG = 9;
-struct V4Config { int nt, qpt, G, TS, L, cpx, se_floats, max_clusters; };
-bool v4_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V4Config *out);
-cudaError_t launch_estep_v4(const EStepParams &p, const V4Config &cfg, int n_clusters, cudaStream_t stream);
+// on-chip kernel of the common configuration (estep_onchip.cu): warp-specialised (producer warps stream
+// image t+1 while the compute threads run the selection chain of image t; the scratch holds TWO plane
+// sets per resident cluster), quad (float4) pixel ownership, two class planes resident in tensor memory
+constexpr int OC_NT = 896;            // compute threads per CTA
+constexpr int OC_MAXG = 9;            // largest cluster (non-portable size; 15 of them are co-resident on B200)
+constexpr int OC_PF_AHEAD = 16;       // chunks prefetched into the L2 ahead of the staging ring
+struct OnchipConfig { int nt, qpt, G, TS, L, cpx, se_floats, max_clusters; };
+bool onchip_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, OnchipConfig *out);
+cudaError_t launch_estep_onchip(const EStepParams &p, const OnchipConfig &cfg, int n_clusters, cudaStream_t stream);
 
 struct FinalizeParams {
     float *map; long long s0, s2;

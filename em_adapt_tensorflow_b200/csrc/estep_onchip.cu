@@ -1,4 +1,4 @@
-// estep_v4.cu -- the E-step kernel of the common configuration, fourth generation (sm_100a).
+// estep_onchip.cu -- the E-step kernel of the common configuration, fourth generation (sm_100a).
 //
 // Contract (unchanged from the third generation): one thread-block cluster per image, persistent,
 // images claimed from a counter; suppress_others = true with a margin >= 0, contiguous pixels, the
@@ -37,7 +37,7 @@
 #include "seqsum.cuh"
 
 namespace wl {
-namespace v4 {
+namespace oc {
 
 constexpr int NB = 2048;                // histogram bins
 constexpr int NSB = 64;                 // super bins exchanged through the mailboxes
@@ -48,7 +48,7 @@ constexpr int GCAP = 1024;              // candidates gathered into every CTA
 constexpr int RCMAX = 256;              // up to here the local selection ranks by counting
 constexpr int MBW = 72;                 // mailbox words per CTA per exchange (a multiple of 4)
 constexpr int HT = 512;                 // threads that scan a 2048-bin histogram (4 bins each)
-constexpr int MAXG = V4_MAXG;
+constexpr int MAXG = OC_MAXG;
 constexpr int NPW = 4;                  // producer warps per CTA
 constexpr int NST = 8;                  // stages of the staging ring (a multiple of NPW: a stage always belongs
                                         // to the same warp, which then sees its mbarrier phases in order)
@@ -361,7 +361,7 @@ __device__ __forceinline__ const uint32_t (*exchange(Cx<NT_> &c, int n))[MBW] {
     const uint32_t par = c.xround & 1u;
     if (c.G > 1) {
         const int nv = (n + 3) >> 2;
-        if (c.p->flags & V4_F_CLASSIC_XCHG) {
+        if (c.p->flags & OC_F_CLASSIC_XCHG) {
             csync<NT_>();
             for (int i = c.tid; i < c.G * n; i += NT_) {
                 const int peer = i / n, w = i - peer * n;
@@ -755,7 +755,7 @@ __device__ __forceinline__ void build_big_digest(Cx<NT_> &c, double cpre, double
         const double lo = (double)F::from(f.e), tol = lo * drift_tol<T>::value;
         if (pin - lo < tol || (lo + lo) - (pin + cs) < tol) f.kind = 0;
     }
-    if (c.p->flags & V4_F_NO_DIGEST) { if (f.kind == 1) f.kind = 0; }
+    if (c.p->flags & OC_F_NO_DIGEST) { if (f.kind == 1) f.kind = 0; }
     // segment heads: the chunk before me (warp edges through shared memory)
     ChunkFn<T> pv = IO::shfl_up(f, 1);
     if (c.lane == 31) ss->wlast[c.warp] = IO::widen(f);
@@ -864,7 +864,7 @@ __device__ __forceinline__ void compact_digest(Cx<NT_> &c, Digest *out) {
         if (i < nseg) {
             e = big->seg[i];
             if (i == DIG_SEG - 1 && n > DIG_SEG) { e.kind = 0; e.tail = (uint16_t)(NT_ - 1); }
-            inl = (e.kind == 0) && (e.head == e.tail) && !(c.p->flags & V4_F_NO_DIGEST);
+            inl = (e.kind == 0) && (e.head == e.tail) && !(c.p->flags & OC_F_NO_DIGEST);
         }
         const uint32_t bal = __ballot_sync(0xffffffffu, inl);
         if (i < nseg) {
@@ -1225,7 +1225,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
             for (int p = 0; p < c.rank; p++) off += ss->fine[p][fb];
             if (c.tid < 4) ss->gather[L.cnt + c.tid] = 0xffffffffu;
             const uint32_t par = c.xround & 1u;
-            if (c.G > 1 && !(c.p->flags & V4_F_CLASSIC_XCHG)) {
+            if (c.G > 1 && !(c.p->flags & OC_F_CLASSIC_XCHG)) {
                 if (c.tid == 0) mbar_expect_tx(&c.ms->xbar[par], L.cnt * 4u);
                 csync<NT_>();                            // my list is complete, the barrier is armed
                 for (uint32_t i = c.tid; i < (uint32_t)c.G * mine; i += NT_) {
@@ -1247,7 +1247,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
                 csync<NT_>();
             }
             uint32_t key;
-            if (L.cnt <= (uint32_t)RCMAX && !(c.p->flags & V4_F_NO_RANKCOUNT)) key = local_select_rank(c, ss->gather, L.cnt, r);
+            if (L.cnt <= (uint32_t)RCMAX && !(c.p->flags & OC_F_NO_RANKCOUNT)) key = local_select_rank(c, ss->gather, L.cnt, r);
             else { key = local_select_hist(c, ss->gather, L.cnt, r, klo, khi); csync<NT_>(); }
             return __uint_as_float(key);
         }
@@ -1367,7 +1367,7 @@ __device__ __forceinline__ void write_labels(Cx<NT_> &c, double shift) {
     // spacing of the floats around the shifted values: guard = 2^-22 * (|best| + |shift|) is at least
     // twice that spacing.  Pixels inside the guard take the exact path.
     const float ashift = __double2float_ru(fabs(shift));
-    const bool exact_all = (p.flags & V4_F_NO_FASTLABEL) != 0;
+    const bool exact_all = (p.flags & OC_F_NO_FASTLABEL) != 0;
     const uint32_t t0 = slot_addr<NT_, QPT>(c, 0), t1 = slot_addr<NT_, QPT>(c, 1 % n_slots(QPT));
     const int r0 = c.res0, r1 = n_slots(QPT) > 1 ? c.res1 : -1;
 #pragma unroll 1
@@ -1445,7 +1445,7 @@ __device__ __forceinline__ void write_labels(Cx<NT_> &c, double shift) {
 // the kernel
 // ---------------------------------------------------------------------------------------------
 template <int NT_, int QPT>
-__global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __grid_constant__ EStepParams p) {
+__global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const __grid_constant__ EStepParams p) {
     typedef Layout<NT_> LY;
     constexpr int NW = NT_ / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1536,7 +1536,8 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
         c.planes = p.planes + (size_t)(slot * 2 + (int)(seq & 1u)) * (size_t)(p.C + 2) * p.Npad;
         c.absmax = c.planes + (size_t)p.C * p.Npad;
         c.absidx = p.absent_idx + (size_t)(slot * 2 + (int)(seq & 1u)) * p.Npad;
-        unsigned long long *prof = p.prof ? p.prof + (size_t)c.b * 8 : nullptr;
+        unsigned long long *prof = p.prof ? p.prof + (size_t)c.b * 32 : nullptr;
+        unsigned long long t_acq = 0ull, t_sel = 0ull, t_fold = 0ull;
         if (prof && lead_thread) prof[0] = gtimer();
         const ImageMeta *im = p.meta + c.b;
         c.mask = im->mask;
@@ -1553,6 +1554,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
         //    zero-margin counts, the tie count and the largest margin): E0 -> shared memory by bulk
         //    copy, the first two planes -> tensor memory meanwhile
         mbar_wait(&ms->ready_bar[seq & 1u], (seq >> 1) & 1u, &p, 404);
+        if (prof && lead_thread) prof[8] = gtimer();
         trc(c, 0, (seq << 8) | 3u);
         trc(c, 1, (uint32_t)c.b);
         const int n_t4 = (c.n_t + 3) & ~3;
@@ -1568,11 +1570,12 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                 mbar_arrive(&ms->e0_bar);
             }
         }
-        if (!(p.flags & V4_F_NO_RESIDENT)) {
+        if (!(p.flags & OC_F_NO_RESIDENT)) {
             plane_load<NT_, QPT>(c, 0, 0);
             c.res0 = 0;
             if (n_slots(QPT) > 1 && c.P > 1) { plane_load<NT_, QPT>(c, 1, 1); c.res1 = 1; c.mru = 1; }
         }
+        if (prof && lead_thread) prof[9] = gtimer();
         {   // both histograms start every image cleared (in CTA 0 the incoming digests of the previous image lay there)
             uint4 *h4 = reinterpret_cast<uint4 *>(sel(c)->hist);
             for (int i = c.tid; i < 2 * NBX / 4; i += NT_) h4[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -1587,6 +1590,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
         double tile_total;
         double cs0;
         const double cpre0 = chunk_prefix(c, &tile_total, &cs0);
+        if (prof && lead_thread) prof[10] = gtimer();
         if (c.tid < 6) {
             uint32_t v = 0u;
             for (int w = 0; w < NPW; w++) {
@@ -1619,9 +1623,11 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                 ms->zlb[c.tid] = z;
             }
         }
+        if (prof && lead_thread) prof[11] = gtimer();
         // 3. mean_max_0 (weaklabel.cpp:69-80): the digest of my tile's float running sum; CTA 0 walks its own
         //    tile at once (no incoming state), the other tiles follow at the end of the image
         build_big_digest<float, NT_>(c, cpre0, cs0, before0);
+        if (prof && lead_thread) prof[12] = gtimer();
         if (c.warp == 0) {
             if (c.rank == 0) {
                 const BigDigest *big = &sums(c)->big;
@@ -1658,10 +1664,14 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                     nsel++;
                     trc(c, 0, (seq << 8) | 7u);
                     trc(c, 2, ((uint32_t)j << 8) | (uint32_t)t);
+                    unsigned long long tq0 = 0ull, tq1 = 0ull, tq2 = 0ull;
+                    if (prof && lead_thread) tq0 = gtimer();
                     const int sl = plane_acquire<NT_, QPT>(c, plane);
                     const uint32_t ta = slot_addr<NT_, QPT>(c, sl);
                     uint32_t zeros;
+                    if (prof && lead_thread) tq1 = gtimer();
                     bias = select_margin<NT_, QPT>(c, ta, k, dmax_bound, &zeros);
+                    if (prof && lead_thread) { tq2 = gtimer(); t_acq += tq1 - tq0; t_sel += tq2 - tq1; }
                     if (bias != 0.f) {
                         // fold: x += bias (weaklabel.cpp:90-92), E = max(E, x) (:94-99)
                         uint32_t gall = 0u, gnew = 0u, znew = 0u;
@@ -1703,7 +1713,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                             // Pixels that leave the zero-margin set of another class: those the folded class newly
                             // exceeds (it was below the max there) plus, at most, the pixels that ever held an
                             // exact tie at the max.  Folding creates a tie wherever the new score EQUALS the old max.
-                            const uint32_t loss = (p.flags & V4_F_LOOSE_ZEROS) ? gall_s : gnew_s + tie_bound;
+                            const uint32_t loss = (p.flags & OC_F_LOOSE_ZEROS) ? gall_s : gnew_s + tie_bound;
                             tie_bound += znew_s - gall_s;
                             if (c.tid < c.P) {
                                 const uint32_t z = ms->zlb[c.tid];
@@ -1716,11 +1726,12 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                     } else if (zeros != 0xffffffffu) {
                         if (c.tid == 0) ms->zlb[plane] = zeros;       // exact count of zero margins
                     }
-                    if (p.flags & V4_F_NO_RESIDENT) {                 // A/B: no residency across steps
+                    if (p.flags & OC_F_NO_RESIDENT) {                 // A/B: no residency across steps
                         if (sl) { if (c.dirty1) plane_store<NT_, QPT>(c, plane, 1); c.res1 = -1; c.dirty1 = false; }
                         else { if (c.dirty0) plane_store<NT_, QPT>(c, plane, 0); c.res0 = -1; c.dirty0 = false; }
                     }
                     csync<NT_>();
+                    if (prof && lead_thread) t_fold += gtimer() - tq2;
                 }
                 if (lead_thread) p.bias_out[((size_t)c.b * p.num_iter + j) * p.C + t] = bias;
             }
@@ -1732,6 +1743,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
         //    digests of both sums travel to CTA 0, whose first two warps walk them at the same time
         double cs1;
         const double cpre1 = chunk_prefix(c, &tile_total, &cs1);
+        if (prof && lead_thread) { prof[16] = t_acq; prof[17] = t_sel; prof[18] = t_fold; prof[20] = gtimer(); }
         if (c.tid == 32) {
             const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
             uint32_t *ob = outbox(c);
@@ -1743,11 +1755,13 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
             for (int q = 0; q < c.rank; q++)
                 before1 += __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
         }
+        if (prof && lead_thread) prof[21] = gtimer();
         // (after this exchange no CTA of the cluster is inside a selection any more: the selection
         //  scratch of CTA 0, which the incoming digests alias, is free)
         if (c.rank == 0 && c.tid == 0 && c.G > 1) mbar_expect_tx(&ms->dig_bar, (uint32_t)((c.G - 1) * 2 * sizeof(Digest)));
         if (c.tid == 32) mbar_expect_tx(&ms->res_bar, 16u);
         build_big_digest<double, NT_>(c, cpre1, cs1, before1);
+        if (prof && lead_thread) prof[22] = gtimer();
         if (c.rank != 0) {
             if (c.warp == 0) {
                 compact_digest(c, &c.outd[1]);
@@ -1764,7 +1778,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                 const BigDigest *big = &ss->big;
                 double s1 = walk_digest<double>(0.0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.s_E,
                                                 [&](int j) { return c.s_E[j]; });
+                if (prof && lead_thread) prof[23] = gtimer();
                 if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 406);
+                if (prof && lead_thread) prof[24] = gtimer();
                 for (int r = 1; r < c.G; r++) {
                     const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
                     if (n_t_r == 0) break;
@@ -1774,6 +1790,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
                                              [&](int j) { return __uint_as_float(ld_peer(remote + 4u * (uint32_t)j)); });
                 }
                 const unsigned long long bits = (unsigned long long)__double_as_longlong(s1);
+                if (prof && lead_thread) prof[25] = gtimer();
                 if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[1], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
             } else {
                 // the float sum continues from the end of my own tile through the float digests of the peers
@@ -1822,9 +1839,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_v4_kernel(const __gri
 template <int NT_, int QPT>
 static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t stream, int *max_clusters) {
     const size_t smem = Layout<NT_>::total(p.se_floats);
-    cudaError_t e = cudaFuncSetAttribute(estep_v4_kernel<NT_, QPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(estep_onchip_kernel<NT_, QPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(estep_v4_kernel<NT_, QPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    e = cudaFuncSetAttribute(estep_onchip_kernel<NT_, QPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((max_clusters ? 64 : n_clusters) * p.G));
@@ -1840,30 +1857,30 @@ static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t s
     cfg.numAttrs = 1;
     if (max_clusters) {
         int n = 0;
-        e = cudaOccupancyMaxActiveClusters(&n, estep_v4_kernel<NT_, QPT>, &cfg);
+        e = cudaOccupancyMaxActiveClusters(&n, estep_onchip_kernel<NT_, QPT>, &cfg);
         *max_clusters = (e == cudaSuccess) ? n : 0;
         return e;
     }
-    return cudaLaunchKernelEx(&cfg, estep_v4_kernel<NT_, QPT>, p);
+    return cudaLaunchKernelEx(&cfg, estep_onchip_kernel<NT_, QPT>, p);
 }
 
 static cudaError_t dispatch(const EStepParams &p, int qpt, int n_clusters, cudaStream_t stream, int *maxc) {
-    if (qpt == 1) return launch_t<V4_NT, 1>(p, n_clusters, stream, maxc);
-    if (qpt == 3) return launch_t<V4_NT, 3>(p, n_clusters, stream, maxc);
-    if (qpt == 9) return launch_t<V4_NT, 9>(p, n_clusters, stream, maxc);
-    if (qpt == 10) return launch_t<V4_NT, 10>(p, n_clusters, stream, maxc);
+    if (qpt == 1) return launch_t<OC_NT, 1>(p, n_clusters, stream, maxc);
+    if (qpt == 3) return launch_t<OC_NT, 3>(p, n_clusters, stream, maxc);
+    if (qpt == 9) return launch_t<OC_NT, 9>(p, n_clusters, stream, maxc);
+    if (qpt == 10) return launch_t<OC_NT, 10>(p, n_clusters, stream, maxc);
     return cudaErrorInvalidValue;
 }
 
-size_t smem_bytes(int se_floats) { return Layout<V4_NT>::total(se_floats); }
+size_t smem_bytes(int se_floats) { return Layout<OC_NT>::total(se_floats); }
 
-}  // namespace v4
+}  // namespace oc
 
 // Geometry of the v4 kernel for an image of N pixels with C classes and a given cluster size.
-static bool v4_try(int N, int C, int G, int tune_TS, V4Config *out) {
-    const int nt = V4_NT;
+static bool onchip_try(int N, int C, int G, int tune_TS, OnchipConfig *out) {
+    const int nt = OC_NT;
     const int cap = 10 * nt * 4;
-    if (G < 1 || G > V4_MAXG) return false;
+    if (G < 1 || G > OC_MAXG) return false;
     int TS = tune_TS ? tune_TS : (N + G - 1) / G;
     TS = (TS + 3) / 4 * 4;
     if (TS < 4) TS = 4;
@@ -1874,17 +1891,17 @@ static bool v4_try(int N, int C, int G, int tune_TS, V4Config *out) {
     out->G = G;
     out->TS = TS;
     out->L = ((TS + nt - 1) / nt) | 1;                   // odd: conflict-free chunk walks
-    if (out->L > v4::DIG_L) return false;
+    if (out->L > oc::DIG_L) return false;
     out->se_floats = ((TS > nt * out->L ? TS : nt * out->L) + 3) / 4 * 4;
-    int cpx = (v4::STAGE_BYTES - 32) / (4 * C);
+    int cpx = (oc::STAGE_BYTES - 32) / (4 * C);
     if (cpx < 1) return false;
     out->cpx = cpx;
-    if (v4::smem_bytes(out->se_floats) > 232448) return false;
+    if (oc::smem_bytes(out->se_floats) > 232448) return false;
     EStepParams p = {};
     p.G = G;
     p.se_floats = out->se_floats;
     int maxc = 0;
-    if (v4::dispatch(p, out->qpt, 0, nullptr, &maxc) != cudaSuccess || maxc <= 0) {
+    if (oc::dispatch(p, out->qpt, 0, nullptr, &maxc) != cudaSuccess || maxc <= 0) {
         cudaGetLastError();
         return false;
     }
@@ -1895,22 +1912,22 @@ static bool v4_try(int N, int C, int G, int tune_TS, V4Config *out) {
 // tune_G = 0: automatic -- the smallest power-of-two cluster that holds the image (two planes in tensor
 // memory need at most 9 quads per thread); large batches of large images take clusters of 9 (non-portable
 // size): on B200 as many of them are co-resident as clusters of 8 (15), so 135 instead of 120 SMs work.
-bool v4_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, V4Config *out) {
-    if (tune_G) return v4_try(N, C, tune_G, tune_TS, out);
-    const int cap = 9 * V4_NT * 4;
+bool onchip_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, OnchipConfig *out) {
+    if (tune_G) return onchip_try(N, C, tune_G, tune_TS, out);
+    const int cap = 9 * OC_NT * 4;
     int G = 1;
     while (G < 8 && (N + G - 1) / G > cap) G *= 2;
     while (G < 8 && (long long)B * G * 2 <= sms && N / (2 * G) >= 4096) G *= 2;
-    bool ok = v4_try(N, C, G, tune_TS, out);
+    bool ok = onchip_try(N, C, G, tune_TS, out);
     if (G == 8 && tune_TS == 0) {
-        V4Config alt;
-        if (v4_try(N, C, 9, 0, &alt) && (!ok || (alt.max_clusters >= out->max_clusters && B >= alt.max_clusters) || alt.qpt < out->qpt)) { *out = alt; ok = true; }
+        OnchipConfig alt;
+        if (onchip_try(N, C, 9, 0, &alt) && (!ok || (alt.max_clusters >= out->max_clusters && B >= alt.max_clusters) || alt.qpt < out->qpt)) { *out = alt; ok = true; }
     }
     return ok;
 }
 
-cudaError_t launch_estep_v4(const EStepParams &p, const V4Config &cfg, int n_clusters, cudaStream_t stream) {
-    return v4::dispatch(p, cfg.qpt, n_clusters, stream, nullptr);
+cudaError_t launch_estep_onchip(const EStepParams &p, const OnchipConfig &cfg, int n_clusters, cudaStream_t stream) {
+    return oc::dispatch(p, cfg.qpt, n_clusters, stream, nullptr);
 }
 
 }  // namespace wl

@@ -64,25 +64,21 @@ class EStepPlan:
         return self
 
     def set_path(self, path):
-        """0 auto, 1 generic kernel, 5 ("fast") the on-chip path (estep_v4.cu), 4 ("fast3") / 2 ("fast2") / 3 ("fast1") its predecessors (labels() fails if a forced path does not apply)."""
-        _lib.check(self._L.weaklabel_plan_set_path(self.handle, {"auto": 0, "generic": 1, "fast2": 2, "fast1": 3, "fast3": 4, "fast": 5}.get(path, path)))
-        return self
-
-    def set_threads(self, threads_per_cta):
-        """Fast kernel geometry: 0 auto, 1024 (one CTA per SM) or 512 (two CTAs per SM)."""
-        _lib.check(self._L.weaklabel_plan_set_threads(self.handle, int(threads_per_cta)))
+        """"auto" (0), "generic" (1: estep_kernel.cu) or "fast" (2: the on-chip kernel, estep_onchip.cu; labels()
+        fails if it is forced and does not apply)."""
+        _lib.check(self._L.weaklabel_plan_set_path(self.handle, {"auto": 0, "generic": 1, "fast": 2}.get(path, path)))
         return self
 
     def profile(self, enable=True, read=False):
-        """Enable/disable per-image phase stamps; read=True returns the last run's [B,8] uint64 table."""
-        out = np.zeros((self.B, 8), np.uint64) if read else None
+        """Enable/disable per-image phase stamps; read=True returns the last run's [B,32] uint64 table."""
+        out = np.zeros((self.B, 32), np.uint64) if read else None
         _lib.check(self._L.weaklabel_plan_profile(self.handle, int(bool(enable)),
                                                   out.ctypes.data_as(C.c_void_p) if read else None))
         return out
 
     @property
     def last_path(self):
-        return {0: None, 1: "generic", 2: "fast2", 3: "fast1", 4: "fast3", 5: "fast"}[self._L.weaklabel_plan_last_path(self.handle)]
+        return {0: None, 1: "generic", 2: "fast"}[self._L.weaklabel_plan_last_path(self.handle)]
 
     def prepare(self, present, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2,
                 rng=None):

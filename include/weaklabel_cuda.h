@@ -140,27 +140,23 @@ WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *plan, float *d_ma
 WL_API int weaklabel_plan_probes(weaklabel_plan *plan, int *order, float *bias,
                           float *mean0, double *mean1);
 
-/* tuning knobs, mostly for tests: cluster size (0 = auto; 1,2,4,8,9 for the warp-specialised
- * kernel, 1,2,4,8,16 for its predecessors),
- * tile size in pixels (0 = auto), number of resident clusters (0 = auto). */
+/* tuning knobs, mostly for tests: cluster size (0 = auto; 1..9 for the on-chip kernel, the generic
+ * kernel rounds down to 1,2,4,8 or takes 16), tile size in pixels (0 = auto), number of resident
+ * clusters (0 = auto). */
 WL_API int weaklabel_plan_tune(weaklabel_plan *plan, int cluster_size, int tile_pixels,
                         int max_clusters);
-/* Two families of kernels implement the E-step: the on-chip fast path (suppress_others with a
- * margin >= 0, contiguous pixels, image fits the cluster) and the generic one (everything else).
- * path: 0 = choose automatically (default), 1 = force generic, 4 = force the warp-specialised
- * fast kernel (estep_v3.cu; run() fails if it does not apply), 2 / 3 = its second- / first-
- * generation predecessors (kept for A/B measurements and for clusters of 16).
- * weaklabel_plan_last_path: which one the last run() launched. */
+/* Two kernels implement the E-step: the on-chip one (estep_onchip.cu: suppress_others with a
+ * margin >= 0, contiguous pixels, image fits a cluster of <= 9 CTAs) and the generic one
+ * (estep_kernel.cu: everything else).
+ * path: 0 = choose automatically (default), 1 = force generic, 2 = force on-chip (run() fails if
+ * it does not apply).  weaklabel_plan_last_path: which one the last run() launched. */
 WL_API int weaklabel_plan_set_path(weaklabel_plan *plan, int path);
 WL_API int weaklabel_plan_last_path(const weaklabel_plan *plan);
-/* threads per CTA of the second-generation fast kernel: 0 = auto, 1024 (one CTA per SM) or 512
- * (two CTAs per SM, clusters twice as large); a non-zero value deselects the warp-specialised
- * kernel, whose geometry is fixed (896 compute + 128 producer threads). */
-WL_API int weaklabel_plan_set_threads(weaklabel_plan *plan, int threads_per_cta);
-/* Per-image phase time stamps of the fast kernel (globaltimer ns): out[B][8] = {claimed,
- * streamed-in, mean_max_0 done, iterations done, mean_max_1 done, labels written, selections
- * performed, label-set size}.  Reads the stamps of the last run into `out` (may be NULL), then
- * enables (1) / disables (0) stamping for the following runs. */
+/* Per-image phase time stamps of the on-chip kernel (globaltimer ns): out[B][32], [0..7] = {claimed,
+ * streamed-in, mean_max_0 digest done, iterations done, sums known, labels written, selections
+ * performed, label-set size}, [8..31] finer stamps of the lead thread (tools/phase_report.py).
+ * Reads the stamps of the last run into `out` (may be NULL), then enables (1) / disables (0)
+ * stamping for the following runs. */
 WL_API int weaklabel_plan_profile(weaklabel_plan *plan, int enable, unsigned long long *out);
 /* kernels launched by this plan since creation (bench.py's gpu_launches) */
 WL_API long long weaklabel_plan_launches(const weaklabel_plan *plan);

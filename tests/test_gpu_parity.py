@@ -16,8 +16,6 @@ import os
 
 pytestmark = pytest.mark.gpu
 ALL = [c["name"] for c in cases.CASES]
-# WL_TEST_VARIANTS=fast restricts the forced-geometry tests to the current kernel generation
-VARIANTS = os.environ.get("WL_TEST_VARIANTS", "fast,fast3,fast2,fast2-512,fast1").split(",")
 
 
 def _torch():
@@ -36,7 +34,7 @@ def _fast_applies(p):
     return bool(p["suppress_others"]) and p["margin_others"] >= 0
 
 
-def _device_run(f, l, p, tune=None, want_map=True, path="auto", threads=0):
+def _device_run(f, l, p, tune=None, want_map=True, path="auto"):
     torch = _torch()
     B, H, W, C = f.shape
     t = torch.from_numpy(np.ascontiguousarray(f)).cuda()
@@ -44,8 +42,6 @@ def _device_run(f, l, p, tune=None, want_map=True, path="auto", threads=0):
     if tune:
         plan.tune(*tune)
     plan.set_path(path)
-    if threads:
-        plan.set_threads(threads)
     plan.prepare(wl.label_set(l, C), p["suppress_others"], p["num_iter"], p["margin_others"], p["bg"], p["fg"],
                  rng=wl.OrderStream(1))
     lab = plan.labels(t)
@@ -136,45 +132,40 @@ def test_forced_geometries(name, tune):
     assert got_map.tobytes() == want_map.tobytes()
 
 
-FAST_TUNES = [(1, 0, 0), (2, 0, 0), (4, 0, 0), (8, 0, 1), (16, 0, 0), (2, 1200, 0), (1, 4100, 0), (2, 5000, 2)]
+FAST_TUNES = [(1, 0, 0), (2, 0, 0), (4, 0, 0), (8, 0, 1), (9, 0, 0), (3, 0, 2), (2, 1200, 0), (1, 4100, 0), (2, 5000, 2)]
 
 
-@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("tune", FAST_TUNES)
 @pytest.mark.parametrize("name", ["c1_41_p2", "p5_seq3", "p21_41", "allneg_p3", "ties_int", "ties_const", "shape_7x5",
                                   "shape_1x1", "mag_big", "mag_tiny", "rank_last", "c2_41_b30", "shape_100x37"])
-def test_fast_path_forced_geometries(name, tune, variant):
-    """On-chip fast kernels (fast = estep_v4.cu, fast3 = estep_v3.cu, fast2 = estep_v2.cu, fast1 =
-    estep_fast.cu): cluster sizes 1..16 (DSMEM exchange), tiles larger than the image (idle
-    CTAs), the per-thread pixel counts (small tiles select the small builds)."""
+def test_fast_path_forced_geometries(name, tune):
+    """On-chip kernel (estep_onchip.cu): cluster sizes 1..9 (DSMEM exchange), tiles larger than the image
+    (idle CTAs), the per-thread quad counts (small tiles select the small builds)."""
     f, l, p = cases.build_case(name)
     N = f.shape[1] * f.shape[2]
     G, TS, _ = tune
     if TS and G * TS < N:
         pytest.skip("tile tuning does not hold the image")
-    if variant in ("fast", "fast3") and G > 8:
-        pytest.skip("the warp-specialised kernels use clusters of at most 9")
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
-    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(
-        f, l, p, tune=tune, path=variant.split("-")[0], threads=512 if variant.endswith("512") else 0)
+    got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="fast")
     assert bias_g.tobytes() == bias_o.tobytes()
     assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
     assert np.array_equal(got_lab, want_lab)
     assert got_map.tobytes() == want_map.tobytes()
 
 
-@pytest.mark.parametrize("path", [v for v in VARIANTS if v in ("fast", "fast3")])
 @pytest.mark.parametrize("name,tune", [("c3_321_b30", (0, 0, 2)), ("c3_321_b30", (0, 0, 7)), ("c4_513_b4", (9, 0, 1)),
-                                       ("c4_513_b4", (8, 0, 2)), ("c4_513_scale5", (9, 0, 1)), ("c2_41_b30", (9, 0, 3)),
-                                       ("c4_513_p21", (9, 0, 1)), ("p21_41", (3, 0, 1)), ("c3_321_b30", (5, 0, 3))])
-def test_warp_specialised_kernel_cycles_images(name, tune, path):
-    """The warp-specialised kernels with FEWER resident clusters than images: every cluster works through
-    a queue of images while its producer warps stream the next one (staging-ring reuse across images, both
-    plane sets of the scratch, command / ready hand-shake), incl. the non-portable cluster sizes 3, 5, 9."""
+                                       ("c4_513_b4", (9, 0, 2)), ("c4_513_scale5", (9, 0, 1)), ("c2_41_b30", (9, 0, 3)),
+                                       ("c4_513_p21", (9, 0, 1)), ("p21_41", (3, 0, 1)), ("c3_321_b30", (5, 0, 3)),
+                                       ("c3_321_b30", (7, 0, 4)), ("c2_41_b30", (6, 0, 2))])
+def test_onchip_kernel_cycles_images(name, tune):
+    """The on-chip kernel with FEWER resident clusters than images: every cluster works through a queue of
+    images while its producer warps stream the next one (staging-ring reuse across images, both plane sets
+    of the scratch, command / ready hand-shake), incl. the non-portable cluster sizes 3, 5, 6, 7, 9."""
     f, l, p = cases.build_case(name)
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
     for _ in range(2):
-        got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path=path)
+        got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune, path="fast")
         assert bias_g.tobytes() == bias_o.tobytes()
         assert m0_g.tobytes() == m0_o.tobytes() and m1_g.tobytes() == m1_o.tobytes()
         assert np.array_equal(got_lab, want_lab)
@@ -248,19 +239,19 @@ def test_errors_are_reported_not_swallowed():
     plan.close()
 
 
-V4_FLAGS = {"rankcount_off": 1, "resident_off": 2, "fastlabel_off": 4, "loose_zeros": 8, "digest_off": 16,
+OC_FLAGS = {"rankcount_off": 1, "resident_off": 2, "fastlabel_off": 4, "loose_zeros": 8, "digest_off": 16,
             "classic_xchg": 32, "all_off": 63}
 
 
-@pytest.mark.parametrize("flag", sorted(V4_FLAGS))
+@pytest.mark.parametrize("flag", sorted(OC_FLAGS))
 @pytest.mark.parametrize("name,tune", [("p5_seq3", (0, 0, 0)), ("c2_41_b30", (2, 0, 3)), ("ties_int", (4, 0, 0)),
                                        ("mag_tiny", (2, 0, 0)), ("allneg_p3", (0, 0, 0)), ("c3_321_randn", (0, 0, 0)),
                                        ("c4_513_b4", (9, 0, 1))])
 def test_fast_kernel_switches(name, tune, flag, monkeypatch):
-    """Every optimisation of estep_v4.cu has a switch (WEAKLABEL_V4_FLAGS, estep_kernel.cuh V4_F_*) that
+    """Every optimisation of estep_onchip.cu has a switch (WEAKLABEL_FLAGS, estep_kernel.cuh OC_F_*) that
     routes around it: rank-counting selection, planes resident in tensor memory, float label path, tight
     zero-count bound, pushed sum digests, st.async exchanges.  All combinations give the same bits."""
-    monkeypatch.setenv("WEAKLABEL_V4_FLAGS", str(V4_FLAGS[flag]))
+    monkeypatch.setenv("WEAKLABEL_FLAGS", str(OC_FLAGS[flag]))
     f, l, p = cases.build_case(name)
     want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
     got_map, got_lab, (order_g, bias_g, m0_g, m1_g) = _device_run(f, l, p, tune=tune if any(tune) else None, path="fast")
