@@ -57,6 +57,16 @@ def load():
     L.weaklabel_plan_destroy.restype = None
     L.weaklabel_plan_prepare.argtypes = [C.c_void_p, _u8p, C.c_bool, C.c_int, C.c_float, C.c_float,
                                          C.c_float, C.c_void_p]
+    L.weaklabel_plan_prepare_async.argtypes = [C.c_void_p, _u8p, C.c_bool, C.c_int, C.c_float, C.c_float,
+                                               C.c_float, C.c_void_p, C.c_void_p]
+    L.weaklabel_label_set_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.weaklabel_plan_prepare_device_gt.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_bool,
+                                                   C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    L.weaklabel_plan_status.argtypes = [C.c_void_p, _i32p]
+    L.weaklabel_estep_ce_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p]
+    L.weaklabel_estep_labels_dlpack.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.weaklabel_estep_labels_device.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_longlong,
                                                 C.c_void_p, C.c_void_p]
     L.weaklabel_estep_finalize_map_device.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong,
@@ -89,4 +99,6 @@ EXPORTS = ["e_step", "e_step_labels_device", "weaklabel_last_error", "weaklabel_
            "weaklabel_estep_finalize_map_device", "weaklabel_plan_probes", "weaklabel_plan_tune",
            "weaklabel_plan_launches", "weaklabel_plan_set_path", "weaklabel_plan_last_path",
            "weaklabel_plan_profile",
-           "weaklabel_softmax_ce_device"]
+           "weaklabel_softmax_ce_device", "weaklabel_plan_prepare_async", "weaklabel_label_set_device",
+           "weaklabel_plan_prepare_device_gt", "weaklabel_plan_status", "weaklabel_estep_ce_device",
+           "weaklabel_estep_labels_dlpack"]

@@ -9,6 +9,7 @@
 #include <string.h>
 #include <algorithm>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -41,7 +42,7 @@ static int fail(int code, const char *fmt, ...) {
     } while (0)
 
 extern "C" WL_API const char *weaklabel_last_error(void) { return g_err.c_str(); }
-extern "C" WL_API int weaklabel_version(void) { return 100; }
+extern "C" WL_API int weaklabel_version(void) { return 200; }
 extern "C" WL_API int weaklabel_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -204,15 +205,23 @@ struct weaklabel_plan {
     unsigned long long *d_prof; bool prof_on;       // [B][32] phase time stamps
     bool geometry_ok;
     int scratch_slots;
-    int *d_sched;
+    int *d_sched;                   // -> d_tables
     int last_path;
     float *d_planes;
     uint8_t *d_absidx;
     SlotCtl *d_ctl;
     int *d_counter;     // [0] image counter, [1] status
-    ImageMeta *d_meta;
-    uint8_t *d_order;
-    size_t order_cap;
+    ImageMeta *d_meta;              // -> d_tables
+    uint8_t *d_order;               // -> d_tables
+    // label-set tables [sched | meta | order]: ONE device block filled by ONE asynchronous copy out of a
+    // pinned staging buffer; two staging buffers alternate (an event each) so that prepare() never waits
+    // for the device unless it is two uploads ahead
+    unsigned char *d_tables; size_t tables_cap;
+    unsigned char *h_stage[2]; size_t h_stage_cap[2]; cudaEvent_t ev_stage[2]; bool stage_pending[2]; int stage_next;
+    cudaEvent_t ev_tables, ev_run;  // tables uploaded / last kernel of the last run() queued
+    cudaStream_t tables_stream; bool has_tables, has_run;
+    uint32_t *d_masks; int *d_flags; uint32_t *h_masks;   // device label sets (label_set.cu); h_masks pinned [B + 1]
+    std::vector<unsigned char> present_tmp;
     float *d_bias;
     size_t bias_cap;
     float *d_mean0;
@@ -323,11 +332,16 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
     pl->device = device;
     pl->sms = prop.multiProcessorCount;
     cudaError_t e = cudaMalloc(&pl->d_counter, 2 * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc(&pl->d_meta, (size_t)B * sizeof(ImageMeta));
+    if (e == cudaSuccess) e = cudaMemset(pl->d_counter, 0, 2 * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_masks, (size_t)B * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_flags, sizeof(int));
+    if (e == cudaSuccess) e = cudaHostAlloc((void **)&pl->h_masks, (size_t)(B + 1) * sizeof(uint32_t), cudaHostAllocDefault);
+    for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&pl->ev_stage[k], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pl->ev_tables, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pl->ev_run, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean0, (size_t)B * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_mean1, (size_t)B * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_shift, (size_t)B * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&pl->d_sched, (size_t)B * sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&pl->d_prof, (size_t)B * 32 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(pl->d_prof, 0, (size_t)B * 32 * sizeof(unsigned long long));
     if (e != cudaSuccess) {
@@ -342,8 +356,17 @@ extern "C" WL_API void weaklabel_plan_destroy(weaklabel_plan *pl) {
     if (!pl) return;
     cudaSetDevice(pl->device);
     plan_free_geometry(pl);
-    cudaFree(pl->d_counter); cudaFree(pl->d_meta); cudaFree(pl->d_order); cudaFree(pl->d_bias);
-    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift); cudaFree(pl->d_sched); cudaFree(pl->d_prof);
+    if (pl->has_run) cudaStreamSynchronize(pl->last_stream);
+    if (pl->has_tables) cudaStreamSynchronize(pl->tables_stream);
+    cudaFree(pl->d_counter); cudaFree(pl->d_tables); cudaFree(pl->d_bias); cudaFree(pl->d_masks); cudaFree(pl->d_flags);
+    cudaFree(pl->d_mean0); cudaFree(pl->d_mean1); cudaFree(pl->d_shift); cudaFree(pl->d_prof);
+    if (pl->h_masks) cudaFreeHost(pl->h_masks);
+    for (int k = 0; k < 2; k++) {
+        if (pl->h_stage[k]) cudaFreeHost(pl->h_stage[k]);
+        if (pl->ev_stage[k]) cudaEventDestroy(pl->ev_stage[k]);
+    }
+    if (pl->ev_tables) cudaEventDestroy(pl->ev_tables);
+    if (pl->ev_run) cudaEventDestroy(pl->ev_run);
     delete pl;
 }
 
@@ -352,7 +375,7 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
     if (cluster_size < 0 || tile_pixels < 0 || max_clusters < 0 || tile_pixels > TS_MAX)
         return fail(WEAKLABEL_ERR_ARG, "bad tuning values");
     CUDA_TRY(cudaSetDevice(pl->device));
-    if (pl->last_stream || pl->geometry_ok) CUDA_TRY(cudaDeviceSynchronize());
+    if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     plan_free_geometry(pl);
     pl->tune_G = cluster_size; pl->tune_TS = tile_pixels; pl->tune_slots = max_clusters;
     return WEAKLABEL_OK;
@@ -370,18 +393,19 @@ extern "C" WL_API int weaklabel_plan_last_path(const weaklabel_plan *pl) { retur
 extern "C" WL_API int weaklabel_plan_profile(weaklabel_plan *pl, int enable, unsigned long long *out) {
     if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
     CUDA_TRY(cudaSetDevice(pl->device));
-    if (pl->last_stream) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
+    if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     if (out) CUDA_TRY(cudaMemcpy(out, pl->d_prof, (size_t)pl->B * 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     pl->prof_on = enable != 0;
     return WEAKLABEL_OK;
 }
 
-extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned char *present,
-                                      bool suppress_others, int num_iter, float margin_others,
-                                      float bg, float fg, weaklabel_rng *rng) {
+extern "C" WL_API int weaklabel_plan_prepare_async(weaklabel_plan *pl, const unsigned char *present,
+                                            bool suppress_others, int num_iter, float margin_others,
+                                            float bg, float fg, weaklabel_rng *rng, void *stream) {
     if (!pl || !present) return fail(WEAKLABEL_ERR_ARG, "weaklabel_plan_prepare: NULL argument");
     if (num_iter < 0) return fail(WEAKLABEL_ERR_ARG, "num_iter %d < 0", num_iter);
     const int B = pl->B, C = pl->C, N = pl->N;
+    cudaStream_t st = (cudaStream_t)stream;
     // weaklabel.cpp:88 -- float * int product truncated to int
     const int nth_bg = (int)(bg * N), nth_fg = (int)(fg * N);
     // validate every label set before drawing anything from the order stream
@@ -424,26 +448,57 @@ extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned 
             }
     }
     CUDA_TRY(cudaSetDevice(pl->device));
-    if (pl->last_stream) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));   // tables may be in use
+    // one block [sched | meta | order], staged in pinned memory and uploaded with one asynchronous copy
     const size_t osz = pl->h_order.size() > 0 ? pl->h_order.size() : 1;
-    if (osz > pl->order_cap) {
-        cudaFree(pl->d_order); pl->d_order = nullptr;
-        cudaFree(pl->d_bias); pl->d_bias = nullptr;
-        CUDA_TRY(cudaMalloc(&pl->d_order, osz));
-        CUDA_TRY(cudaMalloc(&pl->d_bias, osz * sizeof(float)));
-        pl->order_cap = osz;
+    const size_t off_meta = ((size_t)B * sizeof(int) + 15) & ~(size_t)15;
+    const size_t off_order = off_meta + (size_t)B * sizeof(ImageMeta);
+    const size_t total = (off_order + osz + 15) & ~(size_t)15;
+    const int k = pl->stage_next;
+    pl->stage_next ^= 1;
+    if (pl->stage_pending[k]) {                           // the upload this buffer fed two prepares ago
+        CUDA_TRY(cudaEventSynchronize(pl->ev_stage[k]));
+        pl->stage_pending[k] = false;
     }
+    if (total > pl->h_stage_cap[k]) {
+        if (pl->h_stage[k]) cudaFreeHost(pl->h_stage[k]);
+        pl->h_stage[k] = nullptr; pl->h_stage_cap[k] = 0;
+        CUDA_TRY(cudaHostAlloc((void **)&pl->h_stage[k], total + total / 2, cudaHostAllocDefault));
+        pl->h_stage_cap[k] = total + total / 2;
+    }
+    unsigned char *h = pl->h_stage[k];
     {   // claim order: largest label sets first (longest jobs first keeps the tail short)
-        std::vector<int> sched(B);
+        int *sched = reinterpret_cast<int *>(h);
         for (int b = 0; b < B; b++) sched[b] = b;
-        std::stable_sort(sched.begin(), sched.end(),
-                         [&](int a, int b2) { return pl->h_meta[a].P > pl->h_meta[b2].P; });
-        CUDA_TRY(cudaMemcpy(pl->d_sched, sched.data(), (size_t)B * sizeof(int), cudaMemcpyHostToDevice));
+        std::stable_sort(sched, sched + B, [&](int a, int b2) { return pl->h_meta[a].P > pl->h_meta[b2].P; });
     }
-    CUDA_TRY(cudaMemcpy(pl->d_meta, pl->h_meta.data(), (size_t)B * sizeof(ImageMeta), cudaMemcpyHostToDevice));
-    if (!pl->h_order.empty())
-        CUDA_TRY(cudaMemcpy(pl->d_order, pl->h_order.data(), pl->h_order.size(), cudaMemcpyHostToDevice));
-    CUDA_TRY(cudaMemset(pl->d_bias, 0, osz * sizeof(float)));
+    memcpy(h + off_meta, pl->h_meta.data(), (size_t)B * sizeof(ImageMeta));
+    if (!pl->h_order.empty()) memcpy(h + off_order, pl->h_order.data(), pl->h_order.size());
+    if (total > pl->tables_cap || osz > pl->bias_cap) {   // growth (first prepare, larger num_iter): the old tables may be in use
+        if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
+        if (pl->has_tables) CUDA_TRY(cudaStreamSynchronize(pl->tables_stream));
+        if (total > pl->tables_cap) {
+            cudaFree(pl->d_tables); pl->d_tables = nullptr; pl->tables_cap = 0;
+            CUDA_TRY(cudaMalloc(&pl->d_tables, total + total / 2));
+            pl->tables_cap = total + total / 2;
+        }
+        if (osz > pl->bias_cap) {
+            cudaFree(pl->d_bias); pl->d_bias = nullptr; pl->bias_cap = 0;
+            CUDA_TRY(cudaMalloc(&pl->d_bias, (osz + osz / 2) * sizeof(float)));
+            pl->bias_cap = osz + osz / 2;
+        }
+    }
+    // a kernel of the previous run() on ANOTHER stream may still read the tables: order the upload behind it
+    if (pl->has_run && pl->last_stream != st) CUDA_TRY(cudaStreamWaitEvent(st, pl->ev_run, 0));
+    CUDA_TRY(cudaMemcpyAsync(pl->d_tables, h, total, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaEventRecord(pl->ev_stage[k], st));
+    pl->stage_pending[k] = true;
+    CUDA_TRY(cudaMemsetAsync(pl->d_bias, 0, osz * sizeof(float), st));
+    CUDA_TRY(cudaEventRecord(pl->ev_tables, st));
+    pl->tables_stream = st;
+    pl->has_tables = true;
+    pl->d_sched = reinterpret_cast<int *>(pl->d_tables);
+    pl->d_meta = reinterpret_cast<ImageMeta *>(pl->d_tables + off_meta);
+    pl->d_order = pl->d_tables + off_order;
     pl->num_iter = num_iter;
     pl->suppress = suppress_others ? 1 : 0;
     pl->margin = margin_others;
@@ -451,6 +506,48 @@ extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned 
     pl->nth_fg = nth_fg;
     pl->prepared = true;
     return WEAKLABEL_OK;
+}
+
+extern "C" WL_API int weaklabel_plan_prepare(weaklabel_plan *pl, const unsigned char *present,
+                                      bool suppress_others, int num_iter, float margin_others,
+                                      float bg, float fg, weaklabel_rng *rng) {
+    // the tables go up on the stream of the last run() (or the legacy default stream); run() on any other
+    // stream waits for the upload through an event -- nothing here blocks the host
+    void *st = (pl && pl->has_run) ? (void *)pl->last_stream : nullptr;
+    return weaklabel_plan_prepare_async(pl, present, suppress_others, num_iter, margin_others, bg, fg, rng, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// GT shrink + label sets on the device (deeplab.py:110 + weaklabel.cpp:19-31), label_set.cu
+// ---------------------------------------------------------------------------------------------
+extern "C" WL_API int weaklabel_label_set_device(const void *d_gt, int gt_is_int32, int B, int Hg, int Wg, int H, int W, int C,
+                                          unsigned int *d_masks, int *d_flags, void *stream) {
+    if (!d_gt || !d_masks || !d_flags || B <= 0 || Hg <= 0 || Wg <= 0 || H <= 0 || W <= 0 || C <= 0 || C > WEAKLABEL_MAX_CLASSES)
+        return fail(WEAKLABEL_ERR_ARG, "weaklabel_label_set_device: bad argument");
+    CUDA_TRY(launch_label_set(d_gt, gt_is_int32, B, Hg, Wg, H, W, C, d_masks, d_flags, (cudaStream_t)stream));
+    return WEAKLABEL_OK;
+}
+
+extern "C" WL_API int weaklabel_plan_prepare_device_gt(weaklabel_plan *pl, const void *d_gt, int gt_is_int32, int Hg, int Wg,
+                                                bool suppress_others, int num_iter, float margin_others,
+                                                float bg, float fg, weaklabel_rng *rng, void *stream) {
+    if (!pl || !d_gt) return fail(WEAKLABEL_ERR_ARG, "weaklabel_plan_prepare_device_gt: NULL argument");
+    if (Hg <= 0 || Wg <= 0) return fail(WEAKLABEL_ERR_ARG, "bad ground-truth size %dx%d", Hg, Wg);
+    CUDA_TRY(cudaSetDevice(pl->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int B = pl->B, C = pl->C;
+    CUDA_TRY(launch_label_set(d_gt, gt_is_int32, B, Hg, Wg, pl->H, pl->W, C, pl->d_masks, pl->d_flags, st));
+    pl->launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(pl->h_masks, pl->d_masks, (size_t)B * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(pl->h_masks + B, pl->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    // the class order is drawn on the host from rand() and depends on every label-set size: B + 1 words
+    // come back (the only synchronisation of the prepare path)
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (pl->h_masks[B] & 1u) return fail(WEAKLABEL_ERR_ARG, "negative label in the ground-truth map");
+    pl->present_tmp.assign((size_t)B * C, 0);
+    for (int b = 0; b < B; b++)
+        for (int c = 0; c < C; c++) pl->present_tmp[(size_t)b * C + c] = (pl->h_masks[b] >> c) & 1u;
+    return weaklabel_plan_prepare_async(pl, pl->present_tmp.data(), suppress_others, num_iter, margin_others, bg, fg, rng, stream);
 }
 
 extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const float *d_map,
@@ -497,16 +594,20 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     p.labels = d_labels; p.bias_out = pl->d_bias;
     p.mean0 = pl->d_mean0; p.mean1 = pl->d_mean1; p.shift = pl->d_shift;
     p.prof = pl->prof_on ? pl->d_prof : nullptr;
-    CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, 2 * sizeof(int), st));
+    // the label-set tables were uploaded on another stream: wait for them on this one (device side)
+    if (pl->has_tables && pl->tables_stream != st) CUDA_TRY(cudaStreamWaitEvent(st, pl->ev_tables, 0));
+    CUDA_TRY(cudaMemsetAsync(pl->d_counter, 0, sizeof(int), st));      // image counter; the status word is sticky
     if (path == 2) {
         CUDA_TRY(launch_estep_onchip(p, pl->oc, slots_used, st));
     } else {
         CUDA_TRY(cudaMemsetAsync(pl->d_ctl, 0, (size_t)slots_used * sizeof(SlotCtl), st));
         CUDA_TRY(launch_estep(p, slots_used, st));
     }
+    CUDA_TRY(cudaEventRecord(pl->ev_run, st));
     pl->last_path = path;
     pl->launches += 1;
     pl->last_stream = st;
+    pl->has_run = true;
     return WEAKLABEL_OK;
 }
 
@@ -522,26 +623,44 @@ extern "C" WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *pl, fl
     f.B = pl->B; f.N = pl->N; f.C = pl->C; f.num_iter = pl->num_iter; f.suppress = pl->suppress;
     f.margin = pl->margin; f.meta = pl->d_meta; f.order = pl->d_order; f.bias = pl->d_bias;
     f.shift = pl->d_shift;
+    if (pl->has_run && pl->last_stream != (cudaStream_t)stream)        // biases / shift come from run()'s stream
+        CUDA_TRY(cudaStreamWaitEvent((cudaStream_t)stream, pl->ev_run, 0));
     CUDA_TRY(launch_finalize_map(f, (cudaStream_t)stream));
+    CUDA_TRY(cudaEventRecord(pl->ev_run, (cudaStream_t)stream));
     pl->launches += 1;
     pl->last_stream = (cudaStream_t)stream;
+    pl->has_run = true;
     return WEAKLABEL_OK;
 }
 
-static int plan_check_status(weaklabel_plan *pl) {
-    int st[2] = {0, 0};
-    CUDA_TRY(cudaMemcpy(st, pl->d_counter, sizeof st, cudaMemcpyDeviceToHost));
-    if (st[1] != 0)
+static int plan_check_status(weaklabel_plan *pl, int *code) {      // read and clear
+    int st = 0;
+    CUDA_TRY(cudaMemcpy(&st, pl->d_counter + 1, sizeof st, cudaMemcpyDeviceToHost));
+    if (code) *code = st;
+    if (st != 0) CUDA_TRY(cudaMemset(pl->d_counter + 1, 0, sizeof(int)));
+    if (st != 0)
         return fail(WEAKLABEL_ERR_CUDA, "E-step kernel reported an inconsistent selection (code %d): "
-                    "NaN or Inf in the score map?", st[1]);
+                    "NaN or Inf in the score map?", st);
     return WEAKLABEL_OK;
+}
+
+// The kernels' status word, accumulated over every run() since it was last read: synchronises the plan's last stream
+// and reads ONE int.  0 = fine; 2xx / 3xx = a selection found no consistent rank (NaN / Inf among the
+// scores: the labels of that image are not to be trusted); 4xx = a bounded wait gave up.
+extern "C" WL_API int weaklabel_plan_status(weaklabel_plan *pl, int *code) {
+    if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
+    if (code) *code = 0;
+    if (!pl->has_run) return WEAKLABEL_OK;
+    CUDA_TRY(cudaSetDevice(pl->device));
+    CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
+    return plan_check_status(pl, code);
 }
 
 extern "C" WL_API int weaklabel_plan_probes(weaklabel_plan *pl, int *order, float *bias, float *mean0, double *mean1) {
     if (!pl || !pl->prepared) return fail(WEAKLABEL_ERR_STATE, "plan not prepared");
     CUDA_TRY(cudaSetDevice(pl->device));
-    CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
-    int rc = plan_check_status(pl);
+    if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
+    int rc = plan_check_status(pl, nullptr);
     if (rc) return rc;
     const int B = pl->B, C = pl->C, J = pl->num_iter;
     if (order) {
@@ -560,26 +679,35 @@ extern "C" WL_API int weaklabel_plan_probes(weaklabel_plan *pl, int *order, floa
 }
 
 // ---------------------------------------------------------------------------------------------
-// cached plan for the one-call entry points
+// cached plans for the one-call entry points: a small most-recently-used list keyed by shape and
+// device (train / val shapes alternate without re-creating scratch)
 // ---------------------------------------------------------------------------------------------
 static std::mutex g_mu;
-static weaklabel_plan *g_plan = nullptr;
-static float *g_dmap = nullptr;
-static size_t g_dmap_cap = 0;
+static std::vector<weaklabel_plan *> g_plans;          // front = most recently used
+static const size_t PLAN_CACHE = 6;
 static std::vector<unsigned char> g_present;
 
 static int cached_plan(int B, int H, int W, int C, weaklabel_plan **out) {
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
-    if (g_plan && (g_plan->B != B || g_plan->H != H || g_plan->W != W || g_plan->C != C || g_plan->device != dev)) {
-        weaklabel_plan_destroy(g_plan);
-        g_plan = nullptr;
+    for (size_t i = 0; i < g_plans.size(); i++) {
+        weaklabel_plan *pl = g_plans[i];
+        if (pl->B == B && pl->H == H && pl->W == W && pl->C == C && pl->device == dev) {
+            g_plans.erase(g_plans.begin() + i);
+            g_plans.insert(g_plans.begin(), pl);
+            *out = pl;
+            return WEAKLABEL_OK;
+        }
     }
-    if (!g_plan) {
-        int rc = weaklabel_plan_create(&g_plan, B, H, W, C, dev);
-        if (rc) return rc;
+    weaklabel_plan *pl = nullptr;
+    int rc = weaklabel_plan_create(&pl, B, H, W, C, dev);
+    if (rc) return rc;
+    g_plans.insert(g_plans.begin(), pl);
+    while (g_plans.size() > PLAN_CACHE) {
+        weaklabel_plan_destroy(g_plans.back());
+        g_plans.pop_back();
     }
-    *out = g_plan;
+    *out = pl;
     return WEAKLABEL_OK;
 }
 
@@ -595,6 +723,74 @@ static int check_shape_stride(const int *shape, const int *stride, long long *s0
     return WEAKLABEL_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// the legacy host-pointer path (estep.py:29-31 -> weaklabel.cpp:6-7), pipelined: the batch is cut into
+// blocks of images; block k+1 goes up (H2D) while block k is worked on and block k-1 comes back (D2H),
+// on three streams chained by events, so that PCIe runs full duplex.  Pinned / registered host memory is
+// copied directly; pageable memory (what numpy hands over) goes through a pinned staging ring filled
+// and drained by a few host threads.  The class order is drawn on the host block after block from the
+// process-global rand(), which is exactly the sequence of B consecutive single-image calls.
+// ---------------------------------------------------------------------------------------------
+struct LegacyCtx {
+    int device;
+    cudaStream_t s_in, s_k, s_out;
+    cudaEvent_t ev_in[3], ev_k[3], ev_out[3];
+    float *d_buf[3]; size_t d_cap;
+    unsigned char *h_in[2], *h_out[2]; size_t h_cap;
+    bool ok;
+};
+static LegacyCtx g_lc[16];
+
+static void par_memcpy(void *dst, const void *src, size_t bytes) {
+    const size_t MINB = (size_t)8 << 20;
+    int nt = (int)(bytes / MINB);
+    if (nt > 6) nt = 6;
+    if (nt <= 1) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    const size_t per = ((bytes / nt) + 4095) & ~(size_t)4095;
+    for (int t = 1; t < nt; t++) {
+        const size_t o = (size_t)t * per;
+        if (o >= bytes) break;
+        const size_t n = std::min(per, bytes - o);
+        th.emplace_back([=]() { memcpy((char *)dst + o, (const char *)src + o, n); });
+    }
+    memcpy(dst, src, std::min(per, bytes));
+    for (auto &t : th) t.join();
+}
+
+static int legacy_ctx(LegacyCtx **out) {
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 16) return fail(WEAKLABEL_ERR_ARG, "device %d out of range", dev);
+    LegacyCtx *lc = &g_lc[dev];
+    if (!lc->ok) {
+        lc->device = dev;
+        CUDA_TRY(cudaStreamCreateWithFlags(&lc->s_in, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&lc->s_k, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&lc->s_out, cudaStreamNonBlocking));
+        for (int k = 0; k < 3; k++) {
+            CUDA_TRY(cudaEventCreateWithFlags(&lc->ev_in[k], cudaEventDisableTiming));
+            CUDA_TRY(cudaEventCreateWithFlags(&lc->ev_k[k], cudaEventDisableTiming));
+            CUDA_TRY(cudaEventCreateWithFlags(&lc->ev_out[k], cudaEventDisableTiming));
+        }
+        lc->ok = true;
+    }
+    *out = lc;
+    return WEAKLABEL_OK;
+}
+
+static bool host_pointer_is_pinned(const void *p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+static size_t legacy_block_bytes() {
+    const char *e = getenv("WEAKLABEL_BLOCK_MB");         // tuning knob: size of a pipeline block
+    const long mb = e ? atol(e) : 96;
+    return (size_t)(mb > 0 ? mb : 96) << 20;
+}
+
 static int legacy_impl(float *map, const int *shape, const int *stride, const int *label,
                        bool suppress_others, int num_iter, float margin_others, float bg, float fg) {
     if (!map || !label) return fail(WEAKLABEL_ERR_ARG, "map/label is NULL");
@@ -605,31 +801,111 @@ static int legacy_impl(float *map, const int *shape, const int *stride, const in
     if (C > WEAKLABEL_MAX_CLASSES) return fail(WEAKLABEL_ERR_ARG, "C=%d > %d", C, WEAKLABEL_MAX_CLASSES);
     if (weaklabel_device_count() <= 0)
         return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
+    const long long N = (long long)H * W;
+    if (B > 1 && s0 < (N - 1) * s2 + C) return fail(WEAKLABEL_ERR_ARG, "batch stride %d overlaps images", stride[0]);
     std::lock_guard<std::mutex> lock(g_mu);
-    weaklabel_plan *pl = nullptr;
-    rc = cached_plan(B, H, W, C, &pl);
+    LegacyCtx *lc = nullptr;
+    rc = legacy_ctx(&lc);
     if (rc) return rc;
     g_present.resize((size_t)B * C);
     rc = weaklabel_label_set_host(label, B, H, W, C, g_present.data());
     if (rc) return rc;
-    rc = weaklabel_plan_prepare(pl, g_present.data(), suppress_others, num_iter, margin_others, bg, fg, nullptr);
-    if (rc) return rc;
-    const long long N = (long long)H * W;
-    if (B > 1 && s0 < (N - 1) * s2 + C) return fail(WEAKLABEL_ERR_ARG, "batch stride %d overlaps images", stride[0]);
-    const size_t span = ((size_t)(B - 1) * (size_t)s0 + (size_t)(N - 1) * (size_t)s2 + (size_t)C) * sizeof(float);
-    if (span > g_dmap_cap) {
-        cudaFree(g_dmap); g_dmap = nullptr; g_dmap_cap = 0;
-        CUDA_TRY(cudaMalloc(&g_dmap, span + 256));
-        g_dmap_cap = span;
+    // validate every label set before a single rand() draw or copy (the reference has no partial results either)
+    for (int b = 0; b < B; b++) {
+        int P = 0;
+        for (int c = 0; c < C; c++) P += g_present[(size_t)b * C + c] ? 1 : 0;
+        if (P == 0) return fail(WEAKLABEL_ERR_EMPTY_SET, "image %d has an empty label set (the reference crashes there, weaklabel.cpp:83)", b);
     }
-    CUDA_TRY(cudaMemcpy(g_dmap, map, span, cudaMemcpyHostToDevice));
-    rc = weaklabel_estep_labels_device(pl, g_dmap, s0, s2, nullptr, nullptr);
-    if (rc) return rc;
-    rc = weaklabel_estep_finalize_map_device(pl, g_dmap, s0, s2, nullptr);
-    if (rc) return rc;
-    CUDA_TRY(cudaMemcpy(map, g_dmap, span, cudaMemcpyDeviceToHost));
-    CUDA_TRY(cudaDeviceSynchronize());
-    return plan_check_status(pl);
+    // blocks of nb images (~96 MB): small enough to overlap, large enough to keep the copies efficient
+    const size_t img_span = ((size_t)(N - 1) * (size_t)s2 + (size_t)C) * sizeof(float);
+    const size_t img_step = (size_t)s0 * sizeof(float);
+    int nb = (int)std::max<size_t>(1, legacy_block_bytes() / std::max<size_t>(img_step, 1));
+    if (nb > B || B <= nb + nb / 2) nb = B;
+    const int nblocks = (B + nb - 1) / nb;
+    const size_t blk_span = (size_t)(nb - 1) * img_step + img_span;
+    if (blk_span + 256 > lc->d_cap) {
+        CUDA_TRY(cudaStreamSynchronize(lc->s_out));
+        for (int k = 0; k < 3; k++) { cudaFree(lc->d_buf[k]); lc->d_buf[k] = nullptr; }
+        lc->d_cap = 0;
+        for (int k = 0; k < (nblocks > 1 ? 3 : 1); k++) CUDA_TRY(cudaMalloc(&lc->d_buf[k], blk_span + 256));
+        lc->d_cap = blk_span + 256;
+    }
+    for (int k = 0; k < (nblocks > 1 ? 3 : 1); k++)
+        if (!lc->d_buf[k]) CUDA_TRY(cudaMalloc(&lc->d_buf[k], lc->d_cap));
+    const bool pinned = host_pointer_is_pinned(map) && host_pointer_is_pinned((const char *)map + (size_t)(B - 1) * img_step + img_span - 1);
+    if (!pinned && blk_span > lc->h_cap) {
+        CUDA_TRY(cudaStreamSynchronize(lc->s_out));
+        for (int k = 0; k < 2; k++) {
+            if (lc->h_in[k]) cudaFreeHost(lc->h_in[k]);
+            if (lc->h_out[k]) cudaFreeHost(lc->h_out[k]);
+            lc->h_in[k] = lc->h_out[k] = nullptr;
+        }
+        lc->h_cap = 0;
+        for (int k = 0; k < (nblocks > 1 ? 2 : 1); k++) {
+            CUDA_TRY(cudaHostAlloc((void **)&lc->h_in[k], blk_span, cudaHostAllocDefault));
+            CUDA_TRY(cudaHostAlloc((void **)&lc->h_out[k], blk_span, cudaHostAllocDefault));
+        }
+        lc->h_cap = blk_span;
+    }
+    if (!pinned)
+        for (int k = 0; k < (nblocks > 1 ? 2 : 1); k++)
+            if (!lc->h_in[k]) {
+                CUDA_TRY(cudaHostAlloc((void **)&lc->h_in[k], lc->h_cap, cudaHostAllocDefault));
+                CUDA_TRY(cudaHostAlloc((void **)&lc->h_out[k], lc->h_cap, cudaHostAllocDefault));
+            }
+    std::vector<weaklabel_plan *> used;
+    auto span_of = [&](int k) { const int n = std::min(nb, B - k * nb); return (size_t)(n - 1) * img_step + img_span; };
+    auto drain = [&](int k) -> int {                      // pageable: block k's result from the staging buffer to the caller
+        CUDA_TRY(cudaEventSynchronize(lc->ev_out[k % 3]));
+        par_memcpy((char *)map + (size_t)k * nb * img_step, lc->h_out[k % 2], span_of(k));
+        return WEAKLABEL_OK;
+    };
+    for (int k = 0; k < nblocks; k++) {
+        const int slot = k % 3, b0 = k * nb, n = std::min(nb, B - b0);
+        char *host = (char *)map + (size_t)b0 * img_step;
+        const size_t span = span_of(k);
+        weaklabel_plan *pl = nullptr;
+        rc = cached_plan(n, H, W, C, &pl);
+        if (rc) return rc;
+        if (std::find(used.begin(), used.end(), pl) == used.end()) used.push_back(pl);
+        // ---- up
+        if (k >= 3) CUDA_TRY(cudaStreamWaitEvent(lc->s_in, lc->ev_out[slot], 0));      // d_buf[slot] read back (block k-3)
+        if (pinned) {
+            CUDA_TRY(cudaMemcpyAsync(lc->d_buf[slot], host, span, cudaMemcpyHostToDevice, lc->s_in));
+        } else {
+            if (k >= 2) CUDA_TRY(cudaEventSynchronize(lc->ev_in[(k - 2) % 3]));         // h_in[k % 2] consumed (block k-2)
+            par_memcpy(lc->h_in[k % 2], host, span);
+            CUDA_TRY(cudaMemcpyAsync(lc->d_buf[slot], lc->h_in[k % 2], span, cudaMemcpyHostToDevice, lc->s_in));
+        }
+        CUDA_TRY(cudaEventRecord(lc->ev_in[slot], lc->s_in));
+        // ---- E-step + in-place map (weaklabel.cpp:108-112) on the compute stream
+        CUDA_TRY(cudaStreamWaitEvent(lc->s_k, lc->ev_in[slot], 0));
+        rc = weaklabel_plan_prepare_async(pl, g_present.data() + (size_t)b0 * C, suppress_others, num_iter, margin_others,
+                                          bg, fg, nullptr, lc->s_k);
+        if (rc) return rc;
+        rc = weaklabel_estep_labels_device(pl, lc->d_buf[slot], s0, s2, nullptr, lc->s_k);
+        if (rc) return rc;
+        rc = weaklabel_estep_finalize_map_device(pl, lc->d_buf[slot], s0, s2, lc->s_k);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(lc->ev_k[slot], lc->s_k));
+        // ---- down
+        CUDA_TRY(cudaStreamWaitEvent(lc->s_out, lc->ev_k[slot], 0));
+        if (pinned) {
+            CUDA_TRY(cudaMemcpyAsync(host, lc->d_buf[slot], span, cudaMemcpyDeviceToHost, lc->s_out));
+        } else {
+            if (k >= 2) { rc = drain(k - 2); if (rc) return rc; }                       // frees h_out[k % 2]
+            CUDA_TRY(cudaMemcpyAsync(lc->h_out[k % 2], lc->d_buf[slot], span, cudaMemcpyDeviceToHost, lc->s_out));
+        }
+        CUDA_TRY(cudaEventRecord(lc->ev_out[slot], lc->s_out));
+    }
+    if (!pinned)
+        for (int k = std::max(0, nblocks - 2); k < nblocks; k++) { rc = drain(k); if (rc) return rc; }
+    CUDA_TRY(cudaStreamSynchronize(lc->s_out));           // our three streams only: the caller's streams are left alone
+    for (weaklabel_plan *pl : used) {
+        rc = plan_check_status(pl, nullptr);
+        if (rc) return rc;
+    }
+    return WEAKLABEL_OK;
 }
 
 extern "C" WL_API float *e_step(float *map, const int *shape, const int *stride, const int *label,
@@ -663,7 +939,7 @@ extern "C" WL_API int e_step_labels_device(const float *d_map, const int *shape,
     g_present.resize((size_t)B * C);
     rc = weaklabel_label_set_host(h_label, B, H, W, C, g_present.data());
     if (rc) return rc;
-    rc = weaklabel_plan_prepare(pl, g_present.data(), suppress_others, num_iter, margin_others, bg, fg, rng);
+    rc = weaklabel_plan_prepare_async(pl, g_present.data(), suppress_others, num_iter, margin_others, bg, fg, rng, stream);
     if (rc) return rc;
     rc = weaklabel_estep_labels_device(pl, d_map, s0, s2, d_labels, stream);
     if (rc) return rc;
@@ -677,6 +953,21 @@ extern "C" WL_API int e_step_labels_device(const float *d_map, const int *shape,
     return rc;
 }
 
+// ---------------------------------------------------------------------------------------------
+// softmax cross-entropy (deeplab.py:182) and the E-step + loss sequence (deeplab.py:120-123,182)
+// ---------------------------------------------------------------------------------------------
+static int device_sms() {
+    static int sms[16] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return 148;
+    if (!sms[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        sms[dev] = n;
+    }
+    return sms[dev];
+}
+
 extern "C" WL_API int weaklabel_softmax_ce_device(const float *d_logits, const unsigned char *d_labels,
                                            long long n_pix, int C, int ignore_label,
                                            float *d_loss_mean, int *d_valid, float *d_dlogits,
@@ -688,6 +979,57 @@ extern "C" WL_API int weaklabel_softmax_ce_device(const float *d_logits, const u
         return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
     int n = 0;
     CUDA_TRY(launch_softmax_ce(d_logits, d_labels, n_pix, C, ignore_label, d_loss_mean, d_valid,
-                               d_dlogits, d_work, (cudaStream_t)stream, &n));
+                               d_dlogits, d_work, -1, device_sms(), (cudaStream_t)stream, &n));
     return WEAKLABEL_OK;
+}
+
+// E-step labels and the loss that consumes them, queued back to back on one stream: the label map goes
+// from the E-step kernel to the loss kernel through the L2, every pixel is kept (the E-step never emits
+// ignore_label), so the loss is ONE launch with the denominator B * H * W known beforehand.
+extern "C" WL_API int weaklabel_estep_ce_device(weaklabel_plan *pl, const float *d_map, unsigned char *d_labels,
+                                         float *d_loss_mean, int *d_valid, float *d_dlogits, void *d_work,
+                                         void *stream) {
+    if (!pl || !d_map || !d_labels || !d_work) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_ce_device: NULL argument");
+    if ((((uintptr_t)d_work) & 7u)) return fail(WEAKLABEL_ERR_ARG, "misaligned work pointer");
+    int rc = weaklabel_estep_labels_device(pl, d_map, (long long)pl->N * pl->C, pl->C, d_labels, stream);
+    if (rc) return rc;
+    const long long n_pix = (long long)pl->B * pl->N;
+    int n = 0;
+    CUDA_TRY(launch_softmax_ce(d_map, d_labels, n_pix, pl->C, 255, d_loss_mean, d_valid, d_dlogits, d_work, n_pix,
+                               pl->sms, (cudaStream_t)stream, &n));
+    pl->launches += n;
+    CUDA_TRY(cudaEventRecord(pl->ev_run, (cudaStream_t)stream));
+    return WEAKLABEL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// DLPack front door: the score map (and the label map) as DLTensor / DLManagedTensor (dlpack.h of
+// dmlc/dlpack, third-party; a DLManagedTensor starts with its DLTensor, so either pointer works)
+// ---------------------------------------------------------------------------------------------
+extern "C" WL_API int weaklabel_estep_labels_dlpack(weaklabel_plan *pl, const void *dl_scores, const void *dl_labels,
+                                             void *stream) {
+    if (!pl || !dl_scores || !dl_labels) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_labels_dlpack: NULL argument");
+    const weaklabel_dltensor *s = (const weaklabel_dltensor *)dl_scores, *l = (const weaklabel_dltensor *)dl_labels;
+    if (s->device_type != 2 || l->device_type != 2)       // kDLCUDA
+        return fail(WEAKLABEL_ERR_ARG, "DLPack tensors must live in CUDA device memory (device_type 2), got %d / %d",
+                    s->device_type, l->device_type);
+    if (s->device_id != pl->device || l->device_id != pl->device)
+        return fail(WEAKLABEL_ERR_ARG, "DLPack tensors are on device %d / %d, the plan on %d", s->device_id, l->device_id, pl->device);
+    if (s->dtype_code != 2 || s->dtype_bits != 32 || s->dtype_lanes != 1) return fail(WEAKLABEL_ERR_ARG, "scores must be float32");
+    if (l->dtype_code != 1 || l->dtype_bits != 8 || l->dtype_lanes != 1) return fail(WEAKLABEL_ERR_ARG, "labels must be uint8");
+    if (s->ndim != 4 || s->shape[0] != pl->B || s->shape[1] != pl->H || s->shape[2] != pl->W || s->shape[3] != pl->C)
+        return fail(WEAKLABEL_ERR_ARG, "scores must have shape [%d,%d,%d,%d]", pl->B, pl->H, pl->W, pl->C);
+    if (l->ndim != 3 || l->shape[0] != pl->B || l->shape[1] != pl->H || l->shape[2] != pl->W)
+        return fail(WEAKLABEL_ERR_ARG, "labels must have shape [%d,%d,%d]", pl->B, pl->H, pl->W);
+    long long bs = (long long)pl->N * pl->C, ps = pl->C;
+    if (s->strides) {                                     // element strides; NULL = compact row-major
+        if (s->strides[3] != 1 || s->strides[1] != (long long)pl->W * s->strides[2])
+            return fail(WEAKLABEL_ERR_ARG, "scores: classes must be contiguous and rows dense");
+        bs = s->strides[0]; ps = s->strides[2];
+    }
+    if (l->strides && (l->strides[2] != 1 || l->strides[1] != pl->W || l->strides[0] != (long long)pl->N))
+        return fail(WEAKLABEL_ERR_ARG, "labels must be contiguous");
+    const float *d_map = (const float *)((const char *)s->data + s->byte_offset);
+    unsigned char *d_lab = (unsigned char *)l->data + l->byte_offset;
+    return weaklabel_estep_labels_device(pl, d_map, bs, ps, d_lab, stream);
 }

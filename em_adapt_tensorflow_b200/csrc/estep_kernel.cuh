@@ -99,8 +99,16 @@ struct FinalizeParams {
 };
 cudaError_t launch_finalize_map(const FinalizeParams &p, cudaStream_t stream);
 
+// valid_known >= 0: the number of kept pixels is known (E-step labels never carry ignore_label): no count
+// pass, a single launch; < 0: counted from the labels first.  work: 16 bytes of device scratch.
 cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long long n_pix, int C,
                               int ignore_label, float *loss_mean, int *valid, float *dlogits,
-                              void *work, cudaStream_t stream, int *n_launches);
+                              void *work, long long valid_known, int sms, cudaStream_t stream, int *n_launches);
+
+// GT shrink + image-level label sets on the device (deeplab.py:110, weaklabel.cpp:19-31): nearest-neighbour
+// resize of a dense [B][Hg][Wg] ground-truth map (uint8 or int32) to [H][W], stride-2 scan, values >= C void;
+// masks[b] = bit c set <=> class c present; flags[0] |= 1 when a negative label was seen.
+cudaError_t launch_label_set(const void *gt, int gt_is_int32, int B, int Hg, int Wg, int H, int W, int C,
+                             uint32_t *masks, int *flags, cudaStream_t stream);
 
 }  // namespace wl

@@ -232,6 +232,17 @@ struct alignas(16) BigDigest {              // the local digest of a tile
     DigEntry seg[BIG_SEG];
 };
 
+// CTA 0 keeps the float digest of its own tile (mean_max_0) for the end of the image, when both sums are
+// walked at the same time: the segments plus the raw terms of the chunks that must be added one by one
+// (the first tile of an image crosses most of the binades).  Ranges whose terms do not fit are read back
+// from the E0 plane in the L2 scratch.
+constexpr int OWN_TERMS = 1280;
+struct alignas(16) OwnDigest {
+    int nseg, pad0, pad1, pad2;
+    DigEntry seg[BIG_SEG];
+    float terms[OWN_TERMS];
+};
+
 struct alignas(16) Misc {
     alignas(16) uint32_t outbox[2][MBW];    // alternating with the exchanges
     double wscr_d[32];
@@ -260,7 +271,6 @@ struct alignas(16) Misc {
     uint32_t lcount;
     uint32_t wcnt[32];
     uint32_t wfirst[32];
-    float state0;                       // CTA 0: float running sum at the end of its own tile
     uint8_t plist[MAXC];
     uint8_t pplist[NPW][MAXC];          // the producers' copy (image t+1)
 };
@@ -298,9 +308,15 @@ template <int NT_> struct Layout {
     static constexpr size_t MBOX_BYTES = 2 * MAXG * MBW * 4;
     static constexpr size_t STAGING_BYTES = (size_t)NST * STAGE_BYTES;
     static size_t total(int se_floats) {
-        return A16((size_t)se_floats * 4) + MBOX_BYTES + A16(sizeof(Misc)) + uni_bytes() + 2 * A16(sizeof(Digest)) + STAGING_BYTES;
+        return A16((size_t)se_floats * 4) + MBOX_BYTES + A16(sizeof(Misc)) + uni_bytes() + 2 * A16(sizeof(Digest)) +
+               A16(sizeof(OwnDigest)) + STAGING_BYTES;
     }
 };
+
+__device__ __forceinline__ unsigned char *smem0() {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    return smem_raw;
+}
 
 template <int NT_> struct Cx {
     const EStepParams *p;
@@ -308,11 +324,16 @@ template <int NT_> struct Cx {
     float *planes;        // scratch of the image in work: [C+2][Npad]
     float *absmax;        // plane C of the scratch (single foreground class only)
     uint8_t *absidx;
-    float *s_E;
-    uint32_t (*mbox)[MAXG][MBW];
-    Misc *ms;
-    unsigned char *uni;
-    Digest *outd;         // [2]: my float and double digests (pushed to CTA 0)
+    // Shared memory is addressed as (dynamic shared base + byte offset), never through pointers kept in
+    // this struct: if the compiler leaves the struct in local memory, a pointer loaded back from there is
+    // a GENERIC pointer and every LDS / ATOMS of the kernel degrades to a generic LD / ATOM.
+    uint32_t o_mbox, o_ms, o_uni, o_outd, o_own;
+    __device__ __forceinline__ float *sE() const { return reinterpret_cast<float *>(smem0()); }
+    __device__ __forceinline__ uint32_t (*mboxp() const)[MAXG][MBW] { return reinterpret_cast<uint32_t (*)[MAXG][MBW]>(smem0() + o_mbox); }
+    __device__ __forceinline__ Misc *msp() const { return reinterpret_cast<Misc *>(smem0() + o_ms); }
+    __device__ __forceinline__ unsigned char *unip() const { return smem0() + o_uni; }
+    __device__ __forceinline__ Digest *outdp() const { return reinterpret_cast<Digest *>(smem0() + o_outd); }     // [2]: my float and double digests (pushed to CTA 0)
+    __device__ __forceinline__ OwnDigest *ownp() const { return reinterpret_cast<OwnDigest *>(smem0() + o_own); }  // CTA 0: float digest of its own tile
     int base, n_t, TQ;    // my tile: pixels [base, base + n_t), TQ = quads that hold a pixel
     uint32_t xround;      // exchanges done (mailbox / outbox / barrier parity), identical in every CTA
     uint32_t hround;      // histogram rounds done (hist buffer parity)
@@ -330,8 +351,8 @@ template <int NT_> struct Cx {
 template <int NT_> __device__ __forceinline__ void trc(const Cx<NT_> &c, int k, uint32_t v) {
     if (c.p->trail && c.tid == 0) c.p->trail[blockIdx.x * 32 + k] = v;
 }
-template <int NT_> __device__ __forceinline__ SelScratch *sel(Cx<NT_> &c) { return reinterpret_cast<SelScratch *>(c.uni); }
-template <int NT_> __device__ __forceinline__ SumScratch *sums(Cx<NT_> &c) { return reinterpret_cast<SumScratch *>(c.uni); }
+template <int NT_> __device__ __forceinline__ SelScratch *sel(Cx<NT_> &c) { return reinterpret_cast<SelScratch *>(c.unip()); }
+template <int NT_> __device__ __forceinline__ SumScratch *sums(Cx<NT_> &c) { return reinterpret_cast<SumScratch *>(c.unip()); }
 
 // Plain cluster-wide barrier of the COMPUTE threads: every CTA arrives on the barrier of every CTA
 // (release at cluster scope after a CTA barrier), then waits on its own.  Two barriers alternate.
@@ -339,7 +360,7 @@ template <int NT_>
 __device__ __forceinline__ void cluster_sync_compute(Cx<NT_> &c) {
     csync<NT_>();
     if (c.G > 1) {
-        uint64_t *bar = &c.ms->sbar[c.csyncs & 1u];
+        uint64_t *bar = &c.msp()->sbar[c.csyncs & 1u];
         if (c.tid < c.G) mbar_arrive_peer(peer_addr(bar, c.tid));
         mbar_wait_cluster(bar, (c.csyncs >> 1) & 1u, c.p, 401);
         c.csyncs++;
@@ -347,7 +368,7 @@ __device__ __forceinline__ void cluster_sync_compute(Cx<NT_> &c) {
 }
 
 // The outbox of the current exchange (written by any compute threads before exchange()).
-template <int NT_> __device__ __forceinline__ uint32_t *outbox(Cx<NT_> &c) { return c.ms->outbox[c.xround & 1u]; }
+template <int NT_> __device__ __forceinline__ uint32_t *outbox(Cx<NT_> &c) { return c.msp()->outbox[c.xround & 1u]; }
 
 // Every CTA hands the first n words of its outbox to every CTA of the cluster (itself included);
 // returns the mailbox that now holds them: box[p][w] = word w of CTA p.
@@ -357,7 +378,7 @@ template <int NT_> __device__ __forceinline__ uint32_t *outbox(Cx<NT_> &c) { ret
 // the next one (which goes to the other barrier / mailbox / outbox) before this barrier is armed.
 template <int NT_>
 __device__ __forceinline__ const uint32_t (*exchange(Cx<NT_> &c, int n))[MBW] {
-    Misc *s = c.ms;
+    Misc *s = c.msp();
     const uint32_t par = c.xround & 1u;
     if (c.G > 1) {
         const int nv = (n + 3) >> 2;
@@ -365,7 +386,7 @@ __device__ __forceinline__ const uint32_t (*exchange(Cx<NT_> &c, int n))[MBW] {
             csync<NT_>();
             for (int i = c.tid; i < c.G * n; i += NT_) {
                 const int peer = i / n, w = i - peer * n;
-                st_peer(peer_addr(&c.mbox[par][c.rank][w], peer), s->outbox[par][w]);
+                st_peer(peer_addr(&c.mboxp()[par][c.rank][w], peer), s->outbox[par][w]);
             }
             cluster_sync_compute(c);
         } else {
@@ -374,17 +395,17 @@ __device__ __forceinline__ const uint32_t (*exchange(Cx<NT_> &c, int n))[MBW] {
             for (int i = c.tid; i < c.G * nv; i += NT_) {
                 const int peer = i / nv, v = i - peer * nv;
                 const uint4 w = *reinterpret_cast<const uint4 *>(&s->outbox[par][4 * v]);
-                st_async_v4(peer_addr(&c.mbox[par][c.rank][4 * v], peer), w, peer_addr(&s->xbar[par], peer));
+                st_async_v4(peer_addr(&c.mboxp()[par][c.rank][4 * v], peer), w, peer_addr(&s->xbar[par], peer));
             }
             mbar_wait(&s->xbar[par], (c.xround >> 1) & 1u, c.p, 402);
         }
     } else {
         csync<NT_>();
-        for (int w = c.tid; w < n; w += NT_) c.mbox[par][0][w] = s->outbox[par][w];
+        for (int w = c.tid; w < n; w += NT_) c.mboxp()[par][0][w] = s->outbox[par][w];
         csync<NT_>();
     }
     c.xround++;
-    return c.mbox[par];
+    return c.mboxp()[par];
 }
 
 template <int NT_>
@@ -395,20 +416,20 @@ __device__ __forceinline__ uint32_t block_excl_scan_u32(Cx<NT_> &c, uint32_t v, 
         uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
         if (c.lane >= o) inc += t;
     }
-    if (c.lane == 31) c.ms->wscr_u[c.warp] = inc;
+    if (c.lane == 31) c.msp()->wscr_u[c.warp] = inc;
     csync<NT_>();
     if (c.warp == 0) {
-        uint32_t w = c.lane < NW ? c.ms->wscr_u[c.lane] : 0u, winc = w;
+        uint32_t w = c.lane < NW ? c.msp()->wscr_u[c.lane] : 0u, winc = w;
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
             if (c.lane >= o) winc += t;
         }
-        c.ms->wscr_u[c.lane] = winc - w;          // exclusive warp offsets
-        if (c.lane == 31) c.ms->bc_u = winc;
+        c.msp()->wscr_u[c.lane] = winc - w;          // exclusive warp offsets
+        if (c.lane == 31) c.msp()->bc_u = winc;
     }
     csync<NT_>();
-    uint32_t r = c.ms->wscr_u[c.warp] + inc - v;
-    *total = c.ms->bc_u;
+    uint32_t r = c.msp()->wscr_u[c.warp] + inc - v;
+    *total = c.msp()->bc_u;
     csync<NT_>();
     return r;
 }
@@ -422,10 +443,10 @@ __device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, doub
         double t = __shfl_up_sync(0xffffffffu, inc, o);
         if (c.lane >= o) inc += t;
     }
-    if (c.lane == 31) c.ms->wscr_d[c.warp] = inc;
+    if (c.lane == 31) c.msp()->wscr_d[c.warp] = inc;
     csync<NT_>();
     // every warp scans the warp totals itself (NW <= 32 values): no second hand-over
-    double w = c.lane < NW ? c.ms->wscr_d[c.lane] : 0.0, winc = w;
+    double w = c.lane < NW ? c.msp()->wscr_d[c.lane] : 0.0, winc = w;
     for (int o = 1; o < 32; o <<= 1) {
         double t = __shfl_up_sync(0xffffffffu, winc, o);
         if (c.lane >= o) winc += t;
@@ -442,8 +463,9 @@ __device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, doub
 // ---------------------------------------------------------------------------------------------
 struct Prod {
     const EStepParams *p;
-    Misc *ms;
-    unsigned char *staging;   // NST stages shared by the producer warps
+    uint32_t o_ms, o_staging; // shared memory by offset (see Cx); NST stages shared by the producer warps
+    __device__ __forceinline__ Misc *msp() const { return reinterpret_cast<Misc *>(smem0() + o_ms); }
+    __device__ __forceinline__ unsigned char *stagingp() const { return smem0() + o_staging; }
     int pw, lane;
     int base, n_t;
     uint32_t nbase;           // chunks of earlier images (stage and parity of chunk q: from nbase + q)
@@ -469,11 +491,11 @@ __device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int 
     const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
     const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
     const int d = (int)((w.nbase + (uint32_t)q) % NST);
-    float *stage = reinterpret_cast<float *>(w.staging + (size_t)d * STAGE_BYTES);
+    float *stage = reinterpret_cast<float *>(w.stagingp() + (size_t)d * STAGE_BYTES);
     const int nh = lead ? min(4 - lead, nfl) : 0;               // floats before the first aligned 16 bytes
     const uint32_t bytes = (uint32_t)((nfl - nh) * 4) & ~15u;   // aligned interior
     const int t0 = nh + (int)(bytes >> 2);                      // first float of the ragged tail
-    uint64_t *bar = &w.ms->full_bar[d];
+    uint64_t *bar = &w.msp()->full_bar[d];
     if (w.lane >= 1 && w.lane <= 3) {
         const int f = w.lane - 1;
         if (f < nh) stage[lead + f] = __ldg(g0 + f);
@@ -499,7 +521,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     const EStepParams &p = *w.p;
     const ImageMeta *im = p.meta + b;
     const int P = im->P;
-    uint8_t *pl = w.ms->pplist[w.pw];
+    uint8_t *pl = w.msp()->pplist[w.pw];
     if (w.lane < MAXC) pl[w.lane] = im->plist[w.lane];
     __syncwarp();
     const int pl0 = pl[0], pl1 = pl[1], pl2 = pl[2], pl3 = pl[3];
@@ -524,8 +546,8 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     for (int q = q0; q < nchunks; q += NPW) {
         const uint32_t n = w.nbase + (uint32_t)q;
         const int d = (int)(n % NST);
-        mbar_wait(&w.ms->full_bar[d], (n / NST) & 1u, &p, 410);
-        const float *stage = reinterpret_cast<const float *>(w.staging + (size_t)d * STAGE_BYTES);
+        mbar_wait(&w.msp()->full_bar[d], (n / NST) & 1u, &p, 410);
+        const float *stage = reinterpret_cast<const float *>(w.stagingp() + (size_t)d * STAGE_BYTES);
         const int npx = min(cpx, w.n_t - q * cpx);
         const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
         const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
@@ -626,7 +648,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
     }
     if (w.lane == 0) {
-        uint32_t *st = w.ms->pstat[par][w.pw];
+        uint32_t *st = w.msp()->pstat[par][w.pw];
         st[0] = zc0; st[1] = zc1; st[2] = zc2; st[3] = zc3; st[4] = dm; st[5] = ties;
     }
 }
@@ -635,10 +657,10 @@ template <int NT_>
 __device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, unsigned char *staging, int slot, int base, int n_t) {
     Prod w;
     w.p = &p;
-    w.ms = ms;
+    w.o_ms = (uint32_t)(reinterpret_cast<unsigned char *>(ms) - smem0());
     w.pw = (int)(threadIdx.x - NT_) >> 5;
     w.lane = threadIdx.x & 31;
-    w.staging = staging;
+    w.o_staging = (uint32_t)(staging - smem0());
     w.base = base;
     w.n_t = n_t;
     w.nbase = 0;
@@ -723,7 +745,7 @@ template <> struct drift_tol<double> { static constexpr double value = 1.0 / 107
 template <int NT_>
 __device__ __forceinline__ double chunk_prefix(Cx<NT_> &c, double *tile_total, double *chunk_sum) {
     const int L = c.p->L;
-    const float *t = c.s_E + c.tid * L;
+    const float *t = c.sE() + c.tid * L;
     double a0 = 0.0, a1 = 0.0;
     int i = 0;
     for (; i + 1 < L; i += 2) { a0 += (double)t[i]; a1 += (double)t[i + 1]; }
@@ -742,14 +764,14 @@ __device__ __forceinline__ void build_big_digest(Cx<NT_> &c, double cpre, double
     typedef fp_traits<T> F;
     typedef FnIO<T> IO;
     constexpr int NW = NT_ / 32;
-    Misc *ms = c.ms;
+    Misc *ms = c.msp();
     SumScratch *ss = sums(c);
     BigDigest *big = &ss->big;
     const int L = c.p->L;
     const int c0 = c.tid * L;
     const int len = max(0, min(L, c.n_t - c0));
     const double pin = before + cpre;
-    ChunkFn<T> f = (len > 0) ? chunk_eval<T>(c.s_E + c0, len, pin) : chunk_identity<T>();
+    ChunkFn<T> f = (len > 0) ? chunk_eval<T>(c.sE() + c0, len, pin) : chunk_identity<T>();
     if (f.kind == 1) {
         // distrust predictions that pass close to a boundary of the binade
         const double lo = (double)F::from(f.e), tol = lo * drift_tol<T>::value;
@@ -871,7 +893,7 @@ __device__ __forceinline__ void compact_digest(Cx<NT_> &c, Digest *out) {
             if (inl) {
                 const int slot = ncross + __popc(bal & ((1u << c.lane) - 1u));
                 if (slot < DIG_CROSS) {
-                    e.cslot = slot;
+                    e.cslot = slot * DIG_L;
                     e.nterms = max(0, min(L, c.n_t - (int)e.head * L));
                 }
             }
@@ -883,12 +905,40 @@ __device__ __forceinline__ void compact_digest(Cx<NT_> &c, Digest *out) {
     __syncwarp();
     // the terms of the crossing chunks
     for (int i = 0; i < nseg; i++) {
-        const int slot = out->seg[i].cslot;
-        if (slot >= 0) {
+        const int off = out->seg[i].cslot;
+        if (off >= 0) {
             const int t0 = (int)out->seg[i].head * L, nt = out->seg[i].nterms;
-            for (int j = c.lane; j < DIG_L; j += 32) out->cross[slot][j] = (j < nt) ? c.s_E[t0 + j] : 0.f;
+            for (int j = c.lane; j < DIG_L; j += 32) out->cross[0][off + j] = (j < nt) ? c.sE()[t0 + j] : 0.f;
         }
     }
+    __syncwarp();
+}
+
+// warp 0 of CTA 0: keep the local (float) digest of my tile together with the raw terms it needs
+template <int NT_>
+__device__ __forceinline__ void keep_own_digest(Cx<NT_> &c) {
+    const BigDigest *big = &sums(c)->big;
+    OwnDigest *own = c.ownp();
+    const int L = c.p->L;
+    const int n = big->nseg;
+    int used = 0;                                        // floats of own->terms in use (uniform over the warp)
+    for (int i = 0; i < n; i++) {
+        DigEntry e = big->seg[i];
+        e.cslot = -1;
+        e.nterms = 0;
+        if (e.kind == 0) {
+            const int t0 = (int)e.head * L, t1 = min(((int)e.tail + 1) * L, c.n_t);
+            const int nt = max(0, t1 - t0), room = (nt + 3) & ~3;
+            if (used + room <= OWN_TERMS) {
+                for (int j = c.lane; j < room; j += 32) own->terms[used + j] = (j < nt) ? c.sE()[t0 + j] : 0.f;
+                e.cslot = used;
+                e.nterms = nt;
+                used += room;
+            }
+        }
+        if (c.lane == 0) own->seg[i] = e;
+    }
+    if (c.lane == 0) own->nseg = n;
     __syncwarp();
 }
 
@@ -908,7 +958,7 @@ __device__ __forceinline__ T add_range(T s, int i0, int i1, int lane, G &&get) {
 // Walk the entries of one digest (all lanes of the warp hold the same state s).  `get(j)` = term j of
 // the tile the digest describes (used for raw ranges and for composites that do not apply).
 template <typename T, typename G>
-__device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, const float (*cross)[DIG_L],
+__device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, const float *cross,
                                          int L, int n_t, int lane, const float *local, G &&get) {
     typedef fp_traits<T> F;
     for (int i = 0; i < nseg; i++) {
@@ -922,7 +972,8 @@ __device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, con
             if (chunk_apply(f, s)) continue;
         }
         if (e.kind == 0 && e.cslot >= 0 && cross != nullptr) {
-            const float4 *t4 = reinterpret_cast<const float4 *>(cross[e.cslot]);
+            const float *tt = cross + e.cslot;                    // cslot: offset of the terms (a multiple of 4 floats)
+            const float4 *t4 = reinterpret_cast<const float4 *>(tt);
             const int m = e.nterms;
             int j = 0;
             for (; j + 4 <= m; j += 4) {
@@ -932,7 +983,7 @@ __device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, con
                 s = F::add(s, (T)v.z);
                 s = F::add(s, (T)v.w);
             }
-            for (; j < m; j++) s = F::add(s, (T)cross[e.cslot][j]);
+            for (; j < m; j++) s = F::add(s, (T)tt[j]);
             continue;
         }
         const int i0 = (int)e.head * L, i1 = min(((int)e.tail + 1) * L, n_t);
@@ -1005,7 +1056,7 @@ __device__ __forceinline__ void hist_pass_win(Cx<NT_> &c, uint32_t ta, int base,
     __syncwarp();
     for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
         if (q < c.TQ) {
-            const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+            const float4 E = *reinterpret_cast<const float4 *>(c.sE() + 4 * q);
             const uint32_t k0 = __float_as_uint(__fsub_rn(E.x, x.x)), k1 = __float_as_uint(__fsub_rn(E.y, x.y));
             const uint32_t k2 = __float_as_uint(__fsub_rn(E.z, x.z)), k3 = __float_as_uint(__fsub_rn(E.w, x.w));
             atomicAdd(&h[k0 ? win_bin(k0, base) : zi], 1u);
@@ -1023,7 +1074,7 @@ template <int NT_, int QPT>
 __device__ __forceinline__ void hist_pass_range(Cx<NT_> &c, uint32_t ta, uint32_t lo, uint32_t hi, int sh, uint32_t *h) {
     for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
         if (q < c.TQ) {
-            const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+            const float4 E = *reinterpret_cast<const float4 *>(c.sE() + 4 * q);
             const uint32_t k0 = __float_as_uint(__fsub_rn(E.x, x.x)), k1 = __float_as_uint(__fsub_rn(E.y, x.y));
             const uint32_t k2 = __float_as_uint(__fsub_rn(E.z, x.z)), k3 = __float_as_uint(__fsub_rn(E.w, x.w));
             if (k0 >= lo && k0 <= hi) atomicAdd(&h[(k0 - lo) >> sh], 1u);
@@ -1040,7 +1091,7 @@ template <int NT_>
 __device__ __forceinline__ Located locate(Cx<NT_> &c, uint32_t r) {
     constexpr int BPT = NB / HT;                // bins per scanning thread (the first HT threads scan)
     constexpr int TPS = SUBB / BPT;             // threads per super bin
-    Misc *s = c.ms;
+    Misc *s = c.msp();
     SelScratch *ss = sel(c);
     uint32_t *h = ss->hist[c.hround & 1u];
     if (c.tid < HT) {   // 64 super-bin sums of my histogram -> outbox
@@ -1109,7 +1160,7 @@ template <int NT_>
 __device__ __forceinline__ uint32_t local_select_hist(Cx<NT_> &c, const uint32_t *keys, uint32_t cnt, uint32_t r,
                                                       uint32_t lo, uint32_t hi) {
     constexpr int BPT = NB / HT;
-    Misc *s = c.ms;
+    Misc *s = c.msp();
     uint32_t *h = sel(c)->lhist;
     for (int guard = 0; guard < 4; guard++) {
         if (lo == hi) break;
@@ -1159,10 +1210,10 @@ __device__ __forceinline__ uint32_t local_select_rank(Cx<NT_> &c, const uint32_t
             lt += (g.x < my) + (g.y < my) + (g.z < my) + (g.w < my);
             eq += (g.x == my) + (g.y == my) + (g.z == my) + (g.w == my);
         }
-        if (lt <= r && r < lt + eq) c.ms->sel_key = my;
+        if (lt <= r && r < lt + eq) c.msp()->sel_key = my;
     }
     csync<NT_>();
-    return c.ms->sel_key;
+    return c.msp()->sel_key;
 }
 
 // The value of rank k (0-based) among the margins E[i] - x[i] of the whole image; the plane is in the
@@ -1208,13 +1259,13 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
             // gather the candidates of the bin into every CTA, in rank order of the CTAs
             for_each_quad<NT_, QPT>(c, ta, [&](int, int q, float4 x) {
                 if (q >= c.TQ) return;
-                const float4 E = *reinterpret_cast<const float4 *>(c.s_E + 4 * q);
+                const float4 E = *reinterpret_cast<const float4 *>(c.sE() + 4 * q);
                 const uint32_t kk[4] = {__float_as_uint(__fsub_rn(E.x, x.x)), __float_as_uint(__fsub_rn(E.y, x.y)),
                                         __float_as_uint(__fsub_rn(E.z, x.z)), __float_as_uint(__fsub_rn(E.w, x.w))};
 #pragma unroll
                 for (int e = 0; e < 4; e++) {
                     if (kk[e] - klo <= khi - klo) {
-                        const uint32_t pos = atomicAdd(&c.ms->lcount, 1u);
+                        const uint32_t pos = atomicAdd(&c.msp()->lcount, 1u);
                         if (pos < (uint32_t)GCAP) ss->mylist[pos] = kk[e];
                     }
                 }
@@ -1226,13 +1277,13 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
             if (c.tid < 4) ss->gather[L.cnt + c.tid] = 0xffffffffu;
             const uint32_t par = c.xround & 1u;
             if (c.G > 1 && !(c.p->flags & OC_F_CLASSIC_XCHG)) {
-                if (c.tid == 0) mbar_expect_tx(&c.ms->xbar[par], L.cnt * 4u);
+                if (c.tid == 0) mbar_expect_tx(&c.msp()->xbar[par], L.cnt * 4u);
                 csync<NT_>();                            // my list is complete, the barrier is armed
                 for (uint32_t i = c.tid; i < (uint32_t)c.G * mine; i += NT_) {
                     const uint32_t peer = i / mine, w = i - peer * mine;
-                    st_async_u32(peer_addr(&ss->gather[off + w], (int)peer), ss->mylist[w], peer_addr(&c.ms->xbar[par], (int)peer));
+                    st_async_u32(peer_addr(&ss->gather[off + w], (int)peer), ss->mylist[w], peer_addr(&c.msp()->xbar[par], (int)peer));
                 }
-                mbar_wait(&c.ms->xbar[par], (c.xround >> 1) & 1u, c.p, 403);
+                mbar_wait(&c.msp()->xbar[par], (c.xround >> 1) & 1u, c.p, 403);
                 c.xround++;
             } else if (c.G > 1) {
                 csync<NT_>();
@@ -1273,19 +1324,23 @@ template <int NT_, int QPT>
 __device__ __forceinline__ void plane_load(Cx<NT_> &c, int plane, int slot) {
     const float *src = c.planes + (size_t)plane * c.p->Npad + c.base;
     const uint32_t ta = slot_addr<NT_, QPT>(c, slot);
+    // every load of the thread is in flight before the first value is used (the plane comes out of the L2)
+    float4 v[QPT];
 #pragma unroll
     for (int k = 0; k < QPT; k++) {
         const int q = k * NT_ + c.tid;
-        float4 v = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);     // quads beyond the tile
-        if (q < c.TQ) {
-            v = __ldcg(reinterpret_cast<const float4 *>(src + 4 * q));
-            if (4 * q + 3 >= c.n_t) {                   // the last quad of the image: padding pixels
-                if (4 * q + 1 >= c.n_t) v.y = -INFINITY;
-                if (4 * q + 2 >= c.n_t) v.z = -INFINITY;
-                v.w = -INFINITY;
-            }
+        v[k] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);         // quads beyond the tile
+        if (q < c.TQ) v[k] = __ldcg(reinterpret_cast<const float4 *>(src + 4 * q));
+    }
+#pragma unroll
+    for (int k = 0; k < QPT; k++) {
+        const int q = k * NT_ + c.tid;
+        if (q < c.TQ && 4 * q + 3 >= c.n_t) {           // the last quad of the image: padding pixels
+            if (4 * q + 1 >= c.n_t) v[k].y = -INFINITY;
+            if (4 * q + 2 >= c.n_t) v[k].z = -INFINITY;
+            v[k].w = -INFINITY;
         }
-        tm_st4(ta + 4 * k, v);                          // warp-collective: every lane, every k
+        tm_st4(ta + 4 * k, v[k]);                       // warp-collective: every lane, every k
     }
     tm_wait_st();
 }
@@ -1352,91 +1407,148 @@ static __device__ __forceinline__ int label_exact(const EStepParams &p, uint32_t
     return bi;
 }
 
+// Pass A -- runs while the two running sums are still being walked, i.e. WITHOUT the re-centring shift
+// (weaklabel.cpp:108-112), of which only an upper bound `ashift` on the magnitude is known.  Two final
+// scores a > b can round to the same float after the shift only if a - b is below the spacing of the
+// floats around the shifted values: guard = 2^-22 * (|best| + |shift|) is at least twice that spacing.
+// Every pixel whose first maximum is safe against that guard gets its label now; the others are
+// returned as a bit per pixel of this thread (bit 4k + e) and decided by pass B with the exact shift.
 template <int NT_, int QPT>
-__device__ __forceinline__ void write_labels(Cx<NT_> &c, double shift) {
+__device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float ashift, int tid_q, uint32_t tm_q) {
+    // (tid_q, tm_q): the thread whose quads are labelled and its tensor-memory columns -- this thread's own, or
+    // those of a walking warp of CTA 0 (same lane quarter, lower columns) served by a proxy warp
     const EStepParams &p = *c.p;
     uint8_t *out = p.labels + (size_t)c.b * p.N + c.base;
-    const bool has_absent = c.P < p.C;
-    if (c.P == 1 && c.ms->plist[0] == 0) {
+    if (c.P == 1 && c.msp()->plist[0] == 0) {
         // background only: every absent class has a higher index and a score <= the background's
-        for (int i = c.tid; i < c.n_t; i += NT_) out[i] = 0;
-        return;
+        for (int i = tid_q; i < c.n_t; i += NT_) out[i] = 0;
+        return 0ull;
     }
+    const bool has_absent = c.P < p.C;
     const bool have_abs = has_absent && c.P == 1;          // suppressed absent maximum was kept
-    // Two final scores a > b can round to the same float after the shift only if a - b is below the
-    // spacing of the floats around the shifted values: guard = 2^-22 * (|best| + |shift|) is at least
-    // twice that spacing.  Pixels inside the guard take the exact path.
-    const float ashift = __double2float_ru(fabs(shift));
     const bool exact_all = (p.flags & OC_F_NO_FASTLABEL) != 0;
-    const uint32_t t0 = slot_addr<NT_, QPT>(c, 0), t1 = slot_addr<NT_, QPT>(c, 1 % n_slots(QPT));
+    const uint32_t t0 = tm_q, t1 = tm_q + (uint32_t)((1 % n_slots(QPT)) * slot_cols(QPT));
     const int r0 = c.res0, r1 = n_slots(QPT) > 1 ? c.res1 : -1;
+    const int cls0 = r0 >= 0 ? c.msp()->plist[r0] : 0, cls1 = r1 >= 0 ? c.msp()->plist[r1] : 0;
+    const bool two_resident = (c.P == 2 && r0 >= 0 && r1 >= 0 && r0 != r1);
+    unsigned long long unsure = 0ull;
 #pragma unroll 1
     for (int k = 0; k < QPT; k++) {
         // tcgen05.ld is warp-collective: both slots are read by every lane for every k
         const float4 s0v = tm_ld4(t0 + 4 * k);
         const float4 s1v = n_slots(QPT) > 1 ? tm_ld4(t1 + 4 * k) : s0v;
-        const int q = k * NT_ + c.tid;
+        const int q = k * NT_ + tid_q;
         if (q >= c.TQ) continue;
-        float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-        float near_[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // largest score strictly below best
-        float lowest[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
-        int bi[4] = {0, 0, 0, 0};
-        for (int pl = 0; pl < c.P; pl++) {
-            float4 v;
-            if (r0 == pl) v = s0v;
-            else if (r1 == pl) v = s1v;
-            else v = __ldcg(reinterpret_cast<const float4 *>(c.planes + (size_t)pl * p.Npad + c.base + 4 * q));
-            const float vv[4] = {v.x, v.y, v.z, v.w};
-            const int cls = c.ms->plist[pl];
+        const float a0[4] = {s0v.x, s0v.y, s0v.z, s0v.w};
+        const float a1[4] = {s1v.x, s1v.y, s1v.z, s1v.w};
+        uint32_t lab4 = 0u, un4 = 0u;
+        if (two_resident) {
+            // both planes in tensor memory: the first maximum in CLASS order, safe unless the two scores
+            // are distinct and within the guard, or equal (then an absent class may tie after rounding)
+            const int lo_cls = r0 < r1 ? cls0 : cls1, hi_cls = r0 < r1 ? cls1 : cls0;
 #pragma unroll
             for (int e = 0; e < 4; e++) {
-                const float t = vv[e];
-                if (t > best[e]) { near_[e] = best[e]; best[e] = t; bi[e] = cls; }
-                else if (t < best[e]) near_[e] = fmaxf(near_[e], t);
-                lowest[e] = fminf(lowest[e], t);
+                const float lo = r0 < r1 ? a0[e] : a1[e], hi = r0 < r1 ? a1[e] : a0[e];
+                const float guard = __fmul_ru(__fadd_ru(fmaxf(fabsf(lo), fabsf(hi)), ashift), 2.4e-7f);   // > 2^-22
+                const float d = fabsf(__fsub_rn(hi, lo));
+                const bool bad = exact_all || !(d > guard) ;                // d == 0, d <= guard, NaN
+                lab4 |= (uint32_t)(hi > lo ? hi_cls : lo_cls) << (8 * e);
+                un4 |= (bad ? 1u : 0u) << e;
+            }
+        } else {
+            float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            float near_[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // largest score strictly below best
+            int bi[4] = {0, 0, 0, 0};
+            for (int pl = 0; pl < c.P; pl++) {
+                float4 v;
+                if (r0 == pl) v = s0v;
+                else if (r1 == pl) v = s1v;
+                else v = __ldcg(reinterpret_cast<const float4 *>(c.planes + (size_t)pl * p.Npad + c.base + 4 * q));
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+                const int cls = c.msp()->plist[pl];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float t = vv[e];
+                    if (t > best[e]) { near_[e] = best[e]; best[e] = t; bi[e] = cls; }
+                    else if (t < best[e]) near_[e] = fmaxf(near_[e], t);
+                }
+            }
+            float4 av = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+            if (have_abs) av = __ldcg(reinterpret_cast<const float4 *>(c.absmax + c.base + 4 * q));
+            const float ava[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float guard = __fmul_ru(__fadd_ru(fabsf(best[e]), ashift), 2.4e-7f);       // > 2^-22
+                // a distinct score within the guard; or (absent classes exist) every present score equal: a
+                // suppressed absent score is <= the smallest present one and can reach the maximum only then;
+                // or (one present class) the suppressed absent maximum within the guard
+                bool bad = exact_all || !(__fsub_rn(best[e], near_[e]) > guard);
+                if (has_absent && !have_abs && near_[e] == -INFINITY) bad = true;
+                if (have_abs && !(__fsub_rn(best[e], ava[e]) > guard)) bad = true;
+                lab4 |= (uint32_t)bi[e] << (8 * e);
+                un4 |= (bad ? 1u : 0u) << e;
             }
         }
-        float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
-        uchar4 ai = make_uchar4(0, 0, 0, 0);
-        if (have_abs) {
-            av = __ldcg(reinterpret_cast<const float4 *>(c.absmax + c.base + 4 * q));
-            ai = __ldcg(reinterpret_cast<const uchar4 *>(c.absidx + c.base + 4 * q));
-        }
-        const float ava[4] = {av.x, av.y, av.z, av.w};
-        const int aia[4] = {ai.x, ai.y, ai.z, ai.w};
-        const float s0a[4] = {s0v.x, s0v.y, s0v.z, s0v.w};
-        const float s1a[4] = {s1v.x, s1v.y, s1v.z, s1v.w};
+        const int i0 = 4 * q;
 #pragma unroll
+        for (int e = 0; e < 4; e++)
+            if (i0 + e < c.n_t && !((un4 >> e) & 1u)) out[i0 + e] = (uint8_t)(lab4 >> (8 * e));
+        unsure |= (unsigned long long)un4 << (4 * k);
+    }
+    return unsure;
+}
+
+// Pass B -- the pixels pass A left open, now with the exact shift: the reference's own arithmetic
+// (label_exact), one pixel at a time.  Rare, so it is kept OUT of the kernel body: a separate function
+// with plain arguments (inlined, its size kept the compiler from promoting the kernel's context struct to
+// registers, which turned every shared-memory access of the kernel into a generic one).
+struct PassB {
+    const EStepParams *p;
+    const uint8_t *plist;
+    const float *planes, *absmax;
+    const uint8_t *absidx;
+    uint8_t *out;                 // labels of my tile
+    double shift;
+    unsigned long long unsure;
+    uint32_t t0, t1, mask;
+    int r0, r1, b, base, n_t, tid, P, first_absent, nt, qpt, two_slots;
+};
+__device__ __noinline__ void labels_pass_b(const PassB a) {
+    const EStepParams &p = *a.p;
+    const bool have_abs = (a.P < p.C) && a.P == 1;
+#pragma unroll 1
+    for (int k = 0; k < a.qpt; k++) {
+        const uint32_t nib = (uint32_t)(a.unsure >> (4 * k)) & 15u;
+        if (!__any_sync(0xffffffffu, nib != 0u)) continue;           // warp-uniform: tcgen05.ld is collective
+        const float4 s0v = tm_ld4(a.t0 + 4 * k);
+        const float4 s1v = a.two_slots ? tm_ld4(a.t1 + 4 * k) : s0v;
+        const int q = k * a.nt + a.tid;
+#pragma unroll 1
         for (int e = 0; e < 4; e++) {
             const int i = 4 * q + e;
-            if (i >= c.n_t) continue;
-            const float guard = __fmul_ru(__fadd_ru(fabsf(best[e]), ashift), 2.4e-7f);       // > 2^-22
-            bool slow = exact_all || (__fsub_rn(best[e], near_[e]) <= guard);
+            if (!((nib >> e) & 1u) || i >= a.n_t) continue;
+            const float v0 = e == 0 ? s0v.x : (e == 1 ? s0v.y : (e == 2 ? s0v.z : s0v.w));
+            const float v1 = e == 0 ? s1v.x : (e == 1 ? s1v.y : (e == 2 ? s1v.z : s1v.w));
+            int lab = -1;
             if (have_abs) {
-                // one present class: the suppressed absent maximum is <= its score; it matters on a rounding tie
-                if (exact_all) slow = true;
-                else if (__fsub_rn(best[e], ava[e]) <= guard) {
-                    if (aia[e] == c.first_absent) {
-                        const float fa = __double2float_rn(__dadd_rn((double)ava[e], shift));
-                        const float fb = __double2float_rn(__dadd_rn((double)best[e], shift));
-                        if (fa >= fb) bi[e] = (fa > fb) ? aia[e] : min(aia[e], bi[e]);
-                    } else slow = true;
+                // one present class whose score is v0 (plane 0 is resident): when the lowest absent class holds
+                // the suppressed absent maximum the two shifted floats decide, lowest index on a tie
+                const float ava = __ldcg(a.absmax + a.base + i);
+                const int aia = __ldcg(a.absidx + a.base + i);
+                if (a.r0 == 0 && aia == a.first_absent) {
+                    const float fa = __double2float_rn(__dadd_rn((double)ava, a.shift));
+                    const float fb = __double2float_rn(__dadd_rn((double)v0, a.shift));
+                    const int cls = a.plist[0];
+                    lab = fa > fb ? aia : (fa == fb ? min(aia, cls) : cls);
                 }
-            } else if (has_absent) {
-                // every suppressed absent score is <= the smallest ORIGINAL present score <= the smallest
-                // present final score: an absent class can reach the maximum only if all present classes
-                // round to the same float
-                if (__fsub_rn(best[e], lowest[e]) <= guard) slow = true;
             }
-            if (slow) {
-                const float v0 = s0a[e], v1 = s1a[e];
-                bi[e] = label_exact(p, c.mask, c.b, c.base + i, shift, [&](int pp) {
-                    if (r0 == pp) return v0;
-                    if (r1 == pp) return v1;
-                    return __ldcg(c.planes + (size_t)pp * p.Npad + c.base + i);
+            if (lab < 0)
+                lab = label_exact(p, a.mask, a.b, a.base + i, a.shift, [&](int pp) {
+                    if (a.r0 == pp) return v0;
+                    if (a.r1 == pp) return v1;
+                    return __ldcg(a.planes + (size_t)pp * p.Npad + a.base + i);
                 });
-            }
-            out[i] = (uint8_t)bi[e];
+            a.out[i] = (uint8_t)lab;
         }
     }
 }
@@ -1459,18 +1571,18 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
     const int slot = blockIdx.x / p.G;
     unsigned char *staging;
     {
-        unsigned char *q = smem_raw;
-        c.s_E = reinterpret_cast<float *>(q);
-        q += LY::A16((size_t)p.se_floats * 4);
-        c.mbox = reinterpret_cast<uint32_t (*)[MAXG][MBW]>(q);
-        q += LY::MBOX_BYTES;
-        c.ms = reinterpret_cast<Misc *>(q);
-        q += LY::A16(sizeof(Misc));
-        c.uni = q;
-        q += LY::uni_bytes();
-        c.outd = reinterpret_cast<Digest *>(q);
-        q += 2 * LY::A16(sizeof(Digest));
-        staging = q;
+        size_t o = LY::A16((size_t)p.se_floats * 4);        // the running-max tile sits at offset 0
+        c.o_mbox = (uint32_t)o;
+        o += LY::MBOX_BYTES;
+        c.o_ms = (uint32_t)o;
+        o += LY::A16(sizeof(Misc));
+        c.o_uni = (uint32_t)o;
+        o += LY::uni_bytes();
+        c.o_outd = (uint32_t)o;
+        o += 2 * LY::A16(sizeof(Digest));
+        c.o_own = (uint32_t)o;
+        o += LY::A16(sizeof(OwnDigest));
+        staging = smem_raw + o;
     }
     c.xround = 0;
     c.hround = 0;
@@ -1478,7 +1590,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
     c.base = c.rank * p.TS;
     c.n_t = max(0, min(p.TS, p.N - c.base));
     c.TQ = (c.n_t + 3) >> 2;
-    Misc *ms = c.ms;
+    Misc *const ms = c.msp();
     if (c.tid == 0) {
         for (int d = 0; d < NST; d++) mbar_init(&ms->full_bar[d], 1);
         mbar_init(&ms->e0_bar, 1);
@@ -1565,7 +1677,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                 mbar_expect_tx(&ms->e0_bar, bytes);
                 const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
                 for (uint32_t o = 0; o < bytes; o += 32768u)
-                    bulk_g2s(reinterpret_cast<unsigned char *>(c.s_E) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
+                    bulk_g2s(reinterpret_cast<unsigned char *>(c.sE()) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
             } else {
                 mbar_arrive(&ms->e0_bar);
             }
@@ -1581,7 +1693,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             for (int i = c.tid; i < 2 * NBX / 4; i += NT_) h4[i] = make_uint4(0u, 0u, 0u, 0u);
         }
         mbar_wait(&ms->e0_bar, seq & 1u, &p, 405);
-        for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.s_E[i] = 0.f;      // padding pixels: E = 0
+        for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.sE()[i] = 0.f;      // padding pixels: E = 0
         if (prof && lead_thread) prof[1] = gtimer();
         csync<NT_>();
 
@@ -1605,7 +1717,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             outbox(c)[7] = (uint32_t)(tb >> 32);
         }
         float dmax_bound;
-        double before0 = 0.0;
+        double before0 = 0.0, total0 = 0.0;
         uint32_t tie_bound = 0u;
         {
             const uint32_t (*box)[MBW] = exchange(c, 8);
@@ -1613,8 +1725,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             for (int q = 0; q < c.G; q++) {
                 mx = max(mx, box[q][4]);
                 tie_bound += box[q][5];
-                if (q < c.rank)
-                    before0 += __longlong_as_double((long long)((unsigned long long)box[q][6] | ((unsigned long long)box[q][7] << 32)));
+                const double tq = __longlong_as_double((long long)((unsigned long long)box[q][6] | ((unsigned long long)box[q][7] << 32)));
+                if (q < c.rank) before0 += tq;
+                total0 += tq;
             }
             dmax_bound = __uint_as_float(mx);
             if (c.tid < EAGER_P && c.tid < c.P) {
@@ -1629,14 +1742,8 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         build_big_digest<float, NT_>(c, cpre0, cs0, before0);
         if (prof && lead_thread) prof[12] = gtimer();
         if (c.warp == 0) {
-            if (c.rank == 0) {
-                const BigDigest *big = &sums(c)->big;
-                const float s0 = walk_digest<float>(0.f, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.s_E,
-                                                    [&](int j) { return c.s_E[j]; });
-                if (c.lane == 0) ms->state0 = s0;
-            } else {
-                compact_digest(c, &c.outd[0]);
-            }
+            if (c.rank == 0) keep_own_digest(c);       // walked at the end of the image, next to the double sum
+            else compact_digest(c, &c.outdp()[0]);
         }
         csync<NT_>();
         if (prof && lead_thread) prof[2] = gtimer();
@@ -1679,7 +1786,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                             const float4 xn = make_float4(__fadd_rn(x.x, bias), __fadd_rn(x.y, bias), __fadd_rn(x.z, bias), __fadd_rn(x.w, bias));
                             tm_st4(ta + 4 * kq, xn);                  // warp-collective (quads beyond the tile stay -inf)
                             if (q >= c.TQ) return;
-                            float4 *Ep = reinterpret_cast<float4 *>(c.s_E + 4 * q);
+                            float4 *Ep = reinterpret_cast<float4 *>(c.sE() + 4 * q);
                             float4 E = *Ep;
                             gall += (xn.x > E.x) + (xn.y > E.y) + (xn.z > E.z) + (xn.w > E.w);
                             gnew += (xn.x > E.x && x.x < E.x) + (xn.y > E.y && x.y < E.y) + (xn.z > E.z && x.z < E.z) + (xn.w > E.w && x.w < E.w);
@@ -1749,11 +1856,23 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             uint32_t *ob = outbox(c);
             ob[0] = (uint32_t)tb; ob[1] = (uint32_t)(tb >> 32); ob[2] = 0u; ob[3] = 0u;
         }
-        double before1 = 0.0;
+        double before1 = 0.0, total1 = 0.0;
         {
             const uint32_t (*box)[MBW] = exchange(c, 4);
-            for (int q = 0; q < c.rank; q++)
-                before1 += __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
+            for (int q = 0; q < c.G; q++) {
+                const double tq = __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
+                if (q < c.rank) before1 += tq;
+                total1 += tq;
+            }
+        }
+        // |mean_max_0 - mean_max_1| from the plain (double) sums: the sequential float sum of N positive terms
+        // is within N * 2^-24 < 2 % of the real one, the double one within rounding -- an upper bound of the
+        // shift's magnitude for pass A of the labels (NaN / overflow: no pixel is safe)
+        float ashift;
+        {
+            const double m0 = total0 / (double)p.N, m1 = total1 / (double)p.N;
+            const double ub = fabs(m0 - m1) + 0.02 * fabs(m0) + 1e-30;
+            ashift = (ub == ub && ub < 3.0e38) ? __double2float_ru(ub) : INFINITY;
         }
         if (prof && lead_thread) prof[21] = gtimer();
         // (after this exchange no CTA of the cluster is inside a selection any more: the selection
@@ -1764,11 +1883,11 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (prof && lead_thread) prof[22] = gtimer();
         if (c.rank != 0) {
             if (c.warp == 0) {
-                compact_digest(c, &c.outd[1]);
+                compact_digest(c, &c.outdp()[1]);
                 asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // my digest writes -> visible to the copy engine
                 __syncwarp();
                 if (c.lane == 0) {
-                    bulk_s2peer(peer_addr(&sums(c)->inbound[c.rank][0], 0), &c.outd[0], (uint32_t)(2 * sizeof(Digest)), peer_addr(&ms->dig_bar, 0));
+                    bulk_s2peer(peer_addr(&sums(c)->inbound[c.rank][0], 0), &c.outdp()[0], (uint32_t)(2 * sizeof(Digest)), peer_addr(&ms->dig_bar, 0));
                 }
             }
         } else if (c.warp < 2) {
@@ -1776,38 +1895,59 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             if (c.warp == 0) {
                 // the double sum: my own tile out of my shared memory, then the digests of the peers
                 const BigDigest *big = &ss->big;
-                double s1 = walk_digest<double>(0.0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.s_E,
-                                                [&](int j) { return c.s_E[j]; });
-                if (prof && lead_thread) prof[23] = gtimer();
+                double s1 = walk_digest<double>(0.0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.sE(),
+                                                [&](int j) { return c.sE()[j]; });
+                if (prof && lead_thread) {
+                    prof[23] = gtimer();
+                    int raw = 0;
+                    for (int i = 0; i < big->nseg; i++)
+                        if (big->seg[i].kind == 0) raw += ((int)big->seg[i].tail - (int)big->seg[i].head + 1);
+                    prof[27] = (unsigned long long)big->nseg;
+                    prof[28] = (unsigned long long)raw;
+                    prof[29] = (unsigned long long)big->total;
+                }
                 if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 406);
                 if (prof && lead_thread) prof[24] = gtimer();
                 for (int r = 1; r < c.G; r++) {
                     const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
                     if (n_t_r == 0) break;
                     const Digest *d = &ss->inbound[r][1];
-                    const uint32_t remote = peer_addr(c.s_E, r);
-                    s1 = walk_digest<double>(s1, d->seg, d->nseg, d->cross, L, n_t_r, c.lane, nullptr,
+                    const uint32_t remote = peer_addr(c.sE(), r);
+                    s1 = walk_digest<double>(s1, d->seg, d->nseg, &d->cross[0][0], L, n_t_r, c.lane, nullptr,
                                              [&](int j) { return __uint_as_float(ld_peer(remote + 4u * (uint32_t)j)); });
                 }
                 const unsigned long long bits = (unsigned long long)__double_as_longlong(s1);
                 if (prof && lead_thread) prof[25] = gtimer();
                 if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[1], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
             } else {
-                // the float sum continues from the end of my own tile through the float digests of the peers
-                float s0 = ms->state0;
+                // the float sum: the digest of my own tile kept since the start of the image (raw ranges that
+                // did not fit come back from the E0 plane in the L2), then the float digests of the peers
+                const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad;
+                float s0 = walk_digest<float>(0.f, c.ownp()->seg, c.ownp()->nseg, c.ownp()->terms, L, c.n_t, c.lane, nullptr,
+                                              [&](int j) { return __ldcg(e0 + j); });
                 if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 407);
                 for (int r = 1; r < c.G; r++) {
                     const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
                     if (n_t_r == 0) break;
                     const Digest *d = &ss->inbound[r][0];
-                    const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad + (size_t)r * p.TS;     // E0 plane of tile r (L2)
-                    s0 = walk_digest<float>(s0, d->seg, d->nseg, d->cross, L, n_t_r, c.lane, nullptr,
-                                            [&](int j) { return __ldcg(e0 + j); });
+                    const float *e0r = e0 + (size_t)r * p.TS;                                   // E0 plane of tile r (L2)
+                    s0 = walk_digest<float>(s0, d->seg, d->nseg, &d->cross[0][0], L, n_t_r, c.lane, nullptr,
+                                            [&](int j) { return __ldcg(e0r + j); });
                 }
                 const unsigned long long bits = (unsigned long long)__float_as_uint(s0);
                 if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[0], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
             }
         }
+        // 6. labels, pass A: everything that cannot depend on the rounding of the re-centring is written
+        //    while the two walks run (the walking warps of CTA 0 follow once they are done)
+        unsigned long long unsure = 0ull, unsure_px = 0ull;
+        const bool walker = (c.rank == 0 && c.warp < 2);
+        const bool proxy = (c.rank == 0 && (c.warp == 4 || c.warp == 5));       // same lane quarter as warps 0 / 1
+        if (p.labels && !walker) {
+            unsure = labels_pass_a<NT_, QPT>(c, ashift, c.tid, c.tm);
+            if (proxy) unsure_px = labels_pass_a<NT_, QPT>(c, ashift, c.tid - 128, c.tm - (uint32_t)(4 * QPT));
+        }
+        if (prof && lead_thread) prof[26] = gtimer();
         mbar_wait(&ms->res_bar, seq & 1u, &p, 408);
         const float sum0 = __uint_as_float((uint32_t)ms->sumres[0]);
         const double sum1 = __longlong_as_double((long long)ms->sumres[1]);
@@ -1821,7 +1961,23 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         }
         if (prof && lead_thread) prof[4] = gtimer();
         trc(c, 0, (seq << 8) | 9u);
-        if (p.labels) write_labels<NT_, QPT>(c, shift);
+        //    pass B: the few pixels that need the exact shift
+        if (p.labels && __any_sync(0xffffffffu, (unsure | unsure_px) != 0ull)) {
+            PassB a;
+            a.p = &p; a.plist = ms->plist; a.planes = c.planes; a.absmax = c.absmax; a.absidx = c.absidx;
+            a.out = p.labels + (size_t)c.b * p.N + c.base;
+            a.shift = shift; a.unsure = unsure;
+            a.t0 = slot_addr<NT_, QPT>(c, 0); a.t1 = slot_addr<NT_, QPT>(c, 1 % n_slots(QPT)); a.mask = c.mask;
+            a.r0 = c.res0; a.r1 = n_slots(QPT) > 1 ? c.res1 : -1;
+            a.b = c.b; a.base = c.base; a.n_t = c.n_t; a.tid = c.tid; a.P = c.P; a.first_absent = c.first_absent;
+            a.nt = NT_; a.qpt = QPT; a.two_slots = n_slots(QPT) > 1 ? 1 : 0;
+            labels_pass_b(a);
+            if (proxy) {
+                a.unsure = unsure_px; a.tid = c.tid - 128;
+                a.t0 -= (uint32_t)(4 * QPT); a.t1 -= (uint32_t)(4 * QPT);
+                labels_pass_b(a);
+            }
+        }
         csync<NT_>();
         if (prof && lead_thread) {
             prof[5] = gtimer();

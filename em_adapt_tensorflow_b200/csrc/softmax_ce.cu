@@ -6,31 +6,29 @@
 // out of the mean's denominator.  Labels are constants (tf.py_func / argmax carry no gradient),
 // so dlogits = (softmax(z) - onehot(y)) / n_kept.
 //
-// HBM-bound: 4*C bytes read + 4*C written + 1 label byte per pixel.  The flat float stream is
-// staged through shared memory with 16-byte cp.async so that the 84-byte pixels are read and
-// written fully coalesced; the gradient overwrites the staged logits in place.
+// HBM-bound: 4*C bytes read + 4*C written + 1 label byte per pixel (169 B/pixel at C = 21).  One
+// persistent launch: every CTA walks tiles of 256 pixels through a double-buffered shared-memory
+// ring that the copy engine fills (cp.async.bulk global -> shared, completion on an mbarrier) and
+// drains (cp.async.bulk shared -> global, bulk groups), so both directions move as 21.5 KB bulk
+// transfers and no thread issues a 4-byte store; one thread per pixel works on its 84-byte row in
+// place (row stride C words: conflict-free for odd C).  The loss is reduced in double; the last
+// CTA to finish writes the mean.  When the number of kept pixels is known beforehand (the E-step
+// never emits 255: every pixel is kept) the count pass is skipped and this is the only launch.
 #include <float.h>
 #include <math.h>
 #include "estep_kernel.cuh"
+#include "bulk_tile.cuh"
 
 namespace wl {
 
-constexpr int CE_NT = 256;
+constexpr int CE_NT = 256;          // threads per CTA = pixels per tile
+constexpr int CE_STAGES = 2;
 
-struct CeWork {          // 16 bytes of device scratch
+struct CeWork {                     // 16 bytes of device scratch, zeroed by the call
     double loss_sum;
     int valid;
-    int pad;
+    unsigned int done;
 };
-
-__device__ __forceinline__ void ce_cp_async16(void *smem_dst, const void *gsrc) {
-    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void ce_cp_async4(void *smem_dst, const void *gsrc) {
-    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(gsrc) : "memory");
-}
 
 __global__ void __launch_bounds__(CE_NT) ce_count_kernel(const uint8_t *__restrict__ labels, long long n_pix,
                                                          int C, int ignore_label, CeWork *work) {
@@ -52,98 +50,148 @@ __global__ void __launch_bounds__(CE_NT) ce_count_kernel(const uint8_t *__restri
     }
 }
 
-__global__ void __launch_bounds__(CE_NT) ce_fwd_bwd_kernel(const float *__restrict__ logits,
-                                                           const uint8_t *__restrict__ labels,
-                                                           long long n_pix, int C, int ignore_label,
-                                                           float *__restrict__ dlogits, CeWork *work) {
-    extern __shared__ __align__(16) float s_z[];       // [lead + CE_NT*C (+3)]
+// one pixel: z (its C logits in shared memory) becomes the gradient row; returns the pixel's loss
+__device__ __forceinline__ double ce_pixel(float *z, int C, int y, bool keep, float inv) {
+    if (!keep) {
+        for (int k = 0; k < C; k++) z[k] = 0.f;
+        return 0.0;
+    }
+    float m = z[0];
+    for (int k = 1; k < C; k++) m = fmaxf(m, z[k]);
+    float se = 0.f, others = 0.f;
+    const float zy = z[y];
+    for (int k = 0; k < C; k++) {
+        const float e = ce_exp(z[k] - m);
+        se += e;
+        if (k != y) others += e;
+        z[k] = e;
+    }
+    const float r = inv / se;
+    for (int k = 0; k < C; k++) z[k] = (k == y) ? -others * r : z[k] * r;     // p_y - 1 = -(sum of the others) / se
+    return (double)(logf(se) + m) - (double)zy;
+}
+
+// valid_known >= 0: the number of kept pixels (no count pass ran); < 0: read it from work->valid
+__global__ void __launch_bounds__(CE_NT) ce_fused_kernel(const float *__restrict__ logits, const uint8_t *__restrict__ labels,
+                                                         long long n_pix, int C, int ignore_label, float *__restrict__ dlogits,
+                                                         CeWork *work, float *loss_mean, int *valid_out, long long valid_known,
+                                                         int bulk_ok) {
+    extern __shared__ __align__(128) unsigned char ce_smem[];
+    __shared__ uint64_t full_bar[CE_STAGES];
     __shared__ double ws[CE_NT / 32];
     const int tid = threadIdx.x;
-    const long long pix0 = (long long)blockIdx.x * CE_NT;
-    const int npx = (int)min((long long)CE_NT, n_pix - pix0);
-    const int nfl = npx * C;
-    const float *g0 = logits + pix0 * C;
-    const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
-    {
-        const char *a0 = (const char *)g0 - lead * 4;
-        const int nchunk = (lead + nfl + 3) >> 2;
-        for (int q = tid; q < nchunk; q += CE_NT) {
-            const int first = q * 4 - lead;
-            const char *src = a0 + (size_t)q * 16;
-            char *dst = (char *)s_z + (size_t)q * 16;
-            if (first >= 0 && first + 4 <= nfl) ce_cp_async16(dst, src);
-            else {
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const int fi = first + e;
-                    if (fi >= 0 && fi < nfl) ce_cp_async4(dst + e * 4, src + e * 4);
-                }
-            }
-        }
-        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
-    }
-    const int valid = work->valid;                     // written by ce_count_kernel (earlier launch)
+    const size_t tile_bytes = (size_t)CE_NT * C * sizeof(float);
+    const long long ntiles = (n_pix + CE_NT - 1) / CE_NT;
+    const long long valid = valid_known >= 0 ? valid_known : (long long)work->valid;
     const float inv = valid > 0 ? 1.0f / (float)valid : 0.f;
+    if (tid == 0) {
+        for (int s = 0; s < CE_STAGES; s++) ce_mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
     __syncthreads();
+    // a tile is moved by the copy engine when it is a full tile (1024 * C bytes: a multiple of 16) of 16-byte
+    // aligned tensors; the ragged last tile (and misaligned tensors) take plain coalesced loads / stores
+    auto is_bulk = [&](long long t) { return bulk_ok && (t + 1) * CE_NT <= n_pix; };
+    auto issue = [&](long long t, int s) {              // thread 0
+        if (is_bulk(t)) {
+            ce_mbar_expect_tx(&full_bar[s], (uint32_t)tile_bytes);
+            ce_bulk_g2s(ce_smem + (size_t)s * tile_bytes, logits + t * CE_NT * C, (uint32_t)tile_bytes, &full_bar[s]);
+        }
+    };
     double loss = 0.0;
-    if (tid < npx) {
-        float *z = s_z + lead + tid * C;
-        const int y = labels[pix0 + tid];
-        const bool keep = (y != ignore_label && y < C);
-        if (keep) {
-            float m = z[0];
-            for (int k = 1; k < C; k++) m = fmaxf(m, z[k]);
-            float se = 0.f, others = 0.f;
-            const float zy = z[y];
-            for (int k = 0; k < C; k++) {
-                const float e = expf(z[k] - m);
-                se += e;
-                if (k != y) others += e;
-                z[k] = e;
-            }
-            loss = (double)(logf(se) + m) - (double)zy;
-            const float r = inv / se;
-            for (int k = 0; k < C; k++) z[k] = (k == y) ? -others * r : z[k] * r;
+    long long t = blockIdx.x;
+    if (tid == 0 && t < ntiles) issue(t, 0);
+    uint32_t it = 0;
+    for (; t < ntiles; t += gridDim.x, it++) {
+        const int s = it & 1;
+        float *buf = reinterpret_cast<float *>(ce_smem + (size_t)s * tile_bytes);
+        const long long tn = t + gridDim.x;
+        if (tid == 0 && tn < ntiles) {
+            // the other buffer was handed to the copy engine (store of the previous tile): its reads must be
+            // done before the next load lands in it
+            asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+            issue(tn, s ^ 1);
+        }
+        const long long pix0 = t * CE_NT;
+        const int npx = (int)min((long long)CE_NT, n_pix - pix0);
+        const bool bulk = is_bulk(t);
+        if (bulk) {
+            ce_mbar_wait(&full_bar[s], (it >> 1) & 1u);
         } else {
-            for (int k = 0; k < C; k++) z[k] = 0.f;
+            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+            __syncthreads();
+            const float *g = logits + pix0 * C;
+            for (int f = tid; f < npx * C; f += CE_NT) buf[f] = g[f];
+            __syncthreads();
+        }
+        if (tid < npx) {
+            const int y = labels[pix0 + tid];
+            loss += ce_pixel(buf + tid * C, C, y, y != ignore_label && y < C, inv);
+        }
+        if (dlogits) {
+            if (bulk) {
+                asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");     // my row -> visible to the copy engine
+                __syncthreads();
+                if (tid == 0) ce_bulk_s2g(dlogits + pix0 * C, buf, (uint32_t)tile_bytes);
+            } else {
+                __syncthreads();
+                float *o = dlogits + pix0 * C;
+                for (int f = tid; f < npx * C; f += CE_NT) o[f] = buf[f];
+                __syncthreads();
+            }
+        } else {
+            __syncthreads();                            // buffer free for the load after next
         }
     }
-    __syncthreads();
-    if (dlogits) {
-        float *o = dlogits + pix0 * C;
-        for (int f = tid; f < nfl; f += CE_NT) o[f] = s_z[lead + f];
-    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");      // my stores are complete
     for (int o = 16; o; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
     if ((tid & 31) == 0) ws[tid >> 5] = loss;
     __syncthreads();
     if (tid == 0) {
-        double t = 0.0;
-        for (int w = 0; w < CE_NT / 32; w++) t += ws[w];
-        atomicAdd(&work->loss_sum, t);
+        double tsum = 0.0;
+        for (int w = 0; w < CE_NT / 32; w++) tsum += ws[w];
+        atomicAdd(&work->loss_sum, tsum);
+        __threadfence();
+        const unsigned int prev = atomicAdd(&work->done, 1u);
+        if (prev == gridDim.x - 1) {                    // the last CTA: every partial sum is in
+            __threadfence();
+            const double total = atomicAdd(&work->loss_sum, 0.0);
+            if (loss_mean) *loss_mean = valid > 0 ? (float)(total / (double)valid) : 0.f;
+            if (valid_out) *valid_out = (int)valid;
+        }
     }
-}
-
-__global__ void ce_finish_kernel(const CeWork *work, float *loss_mean, int *valid) {
-    const int v = work->valid;
-    if (loss_mean) *loss_mean = v > 0 ? (float)(work->loss_sum / (double)v) : 0.f;
-    if (valid) *valid = v;
 }
 
 cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long long n_pix, int C,
                               int ignore_label, float *loss_mean, int *valid, float *dlogits,
-                              void *work, cudaStream_t stream, int *n_launches) {
+                              void *work, long long valid_known, int sms, cudaStream_t stream, int *n_launches) {
     CeWork *w = reinterpret_cast<CeWork *>(work);
     cudaError_t e = cudaMemsetAsync(w, 0, sizeof(CeWork), stream);
     if (e != cudaSuccess) return e;
-    if (n_pix > 0) {
-        const long long nb = (n_pix + CE_NT - 1) / CE_NT;
-        const int cgrid = (int)min(nb, (long long)148 * 16);
+    const long long nb = (n_pix + CE_NT - 1) / CE_NT;
+    if (valid_known < 0 && n_pix > 0) {
+        const int cgrid = (int)min(nb, (long long)sms * 8);
         ce_count_kernel<<<cgrid, CE_NT, 0, stream>>>(labels, n_pix, C, ignore_label, w);
-        const size_t smem = ((size_t)CE_NT * C + 8) * sizeof(float);
-        ce_fwd_bwd_kernel<<<(unsigned)nb, CE_NT, smem, stream>>>(logits, labels, n_pix, C, ignore_label, dlogits, w);
-        if (n_launches) *n_launches += 2;
+        if (n_launches) *n_launches += 1;
     }
-    ce_finish_kernel<<<1, 1, 0, stream>>>(w, loss_mean, valid);
+    const size_t tile_bytes = (size_t)CE_NT * C * sizeof(float);
+    const size_t smem = CE_STAGES * tile_bytes;
+    static bool attr_set = false;
+    if (!attr_set) {
+        e = cudaFuncSetAttribute(ce_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(CE_STAGES * CE_NT * MAXC * sizeof(float)));
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    // resident CTAs per SM by shared memory (43 KB per CTA at C = 21 -> 5); one persistent wave
+    int per_sm = (int)(220 * 1024 / (smem + 1024));
+    if (per_sm > 8) per_sm = 8;
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sms * per_sm;
+    if (grid > nb) grid = nb;
+    if (grid < 1) grid = 1;
+    const int bulk_ok = ((((uintptr_t)logits) & 15u) == 0 && (dlogits == nullptr || (((uintptr_t)dlogits) & 15u) == 0)) ? 1 : 0;
+    ce_fused_kernel<<<(unsigned)grid, CE_NT, smem, stream>>>(logits, labels, n_pix, C, ignore_label, dlogits, w, loss_mean,
+                                                             valid, valid_known, bulk_ok);
     if (n_launches) *n_launches += 1;
     return cudaGetLastError();
 }

@@ -82,18 +82,48 @@ class EStepPlan:
 
     def prepare(self, present, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2,
                 rng=None):
+        """Label sets [B,C] (0/1) + the five scalars of weaklabel.cpp:7 + the class order (drawn here, on
+        the host, from `rng` or the process-global rand()).  The tables go up asynchronously on the
+        current torch stream; nothing blocks."""
         p = np.ascontiguousarray(present, dtype=np.uint8)
         assert p.shape == (self.B, self.C)
-        _lib.check(self._L.weaklabel_plan_prepare(
+        _lib.check(self._L.weaklabel_plan_prepare_async(
             self.handle, p.ctypes.data_as(C.POINTER(C.c_ubyte)), bool(suppress_others), int(num_iter),
-            float(margin_others), float(bg), float(fg), rng.handle if rng is not None else None))
+            float(margin_others), float(bg), float(fg), rng.handle if rng is not None else None, self._stream()))
         self.num_iter = int(num_iter)
         return self
 
+    def prepare_from_gt(self, gt, suppress_others=True, num_iter=5, margin_others=1e-5, bg=0.4, fg=0.2, rng=None):
+        """deeplab.py:110 + weaklabel.cpp:19-31 on the device: `gt` is the dense ground-truth map, a CUDA
+        uint8 / int32 tensor [B,Hg,Wg] at ANY resolution; it is shrunk to the score size by nearest
+        neighbour and scanned at stride 2 for the image-level label sets (one small stream sync: the class
+        order is drawn on the host from rand())."""
+        import torch
+        assert gt.is_cuda and gt.is_contiguous() and gt.dim() == 3 and gt.shape[0] == self.B
+        assert gt.dtype in (torch.uint8, torch.int32)
+        _lib.check(self._L.weaklabel_plan_prepare_device_gt(
+            self.handle, gt.data_ptr(), int(gt.dtype == torch.int32), int(gt.shape[1]), int(gt.shape[2]),
+            bool(suppress_others), int(num_iter), float(margin_others), float(bg), float(fg),
+            rng.handle if rng is not None else None, self._stream()))
+        self.num_iter = int(num_iter)
+        return self
+
+    def status(self):
+        """Device-side status of the runs since the last call (0 = fine); raises WeakLabelError when a kernel
+        reported NaN / Inf scores or a lost arrival.  Synchronises the plan's last stream."""
+        code = C.c_int(0)
+        _lib.check(self._L.weaklabel_plan_status(self.handle, C.byref(code)))
+        return code.value
+
     @staticmethod
     def _stream():
-        import torch
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        try:
+            import torch
+            if torch.cuda.is_available():
+                return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        except ImportError:
+            pass
+        return C.c_void_p(0)
 
     def labels(self, fmap, out=None):
         """fmap: CUDA float32 tensor [B,H,W,C] (stride(3)==1, rows contiguous).  -> uint8 [B,H,W]."""
@@ -105,6 +135,36 @@ class EStepPlan:
         _lib.check(self._L.weaklabel_estep_labels_device(self.handle, fmap.data_ptr(), fmap.stride(0),
                                                          fmap.stride(2), out.data_ptr(), self._stream()))
         return out
+
+    def labels_dlpack(self, scores, labels):
+        """The DLPack front door (weaklabel_estep_labels_dlpack): `scores` / `labels` are ANY objects with
+        __dlpack__ (torch, cupy, jax arrays ...) holding float32 [B,H,W,C] / uint8 [B,H,W] CUDA memory.
+        Launches on the current torch stream when torch is there, else on the legacy default stream."""
+        caps = [scores.__dlpack__(), labels.__dlpack__()]
+        get = C.pythonapi.PyCapsule_GetPointer
+        get.restype = C.c_void_p
+        get.argtypes = [C.py_object, C.c_char_p]
+        _lib.check(self._L.weaklabel_estep_labels_dlpack(self.handle, get(caps[0], b"dltensor"), get(caps[1], b"dltensor"),
+                                                         self._stream()))
+        return labels
+
+    def labels_and_loss(self, fmap, labels=None, want_grad=True):
+        """deeplab.py:120-123 + 182 in one call (weaklabel_estep_ce_device): the E-step labels of `fmap`
+        (contiguous CUDA float32 [B,H,W,C], the fc8 logits) and the mean softmax cross-entropy of the same
+        logits against them, plus its gradient.  -> (labels, loss 0-d, valid 0-d int32, dlogits or None)."""
+        import torch
+        assert fmap.is_cuda and fmap.dtype == torch.float32 and fmap.is_contiguous()
+        assert tuple(fmap.shape) == (self.B, self.H, self.W, self.C)
+        if labels is None:
+            labels = torch.empty((self.B, self.H, self.W), dtype=torch.uint8, device=fmap.device)
+        loss = torch.empty((), dtype=torch.float32, device=fmap.device)
+        valid = torch.empty((), dtype=torch.int32, device=fmap.device)
+        grad = torch.empty_like(fmap) if want_grad else None
+        work = torch.empty(2, dtype=torch.float64, device=fmap.device)
+        _lib.check(self._L.weaklabel_estep_ce_device(self.handle, fmap.data_ptr(), labels.data_ptr(), loss.data_ptr(),
+                                                     valid.data_ptr(), grad.data_ptr() if want_grad else None,
+                                                     work.data_ptr(), self._stream()))
+        return labels, loss, valid, grad
 
     def finalize_map(self, fmap):
         """In place: fmap becomes what the reference's e_step leaves in `map`."""
@@ -137,6 +197,20 @@ class EStepPlan:
             self.close()
         except Exception:
             pass
+
+
+def label_set_device(gt, H, W, num_classes):
+    """Image-level label sets of a dense CUDA ground-truth map [B,Hg,Wg] (uint8 / int32) shrunk to HxW
+    (deeplab.py:110, weaklabel.cpp:19-31) -> int32 CUDA tensor [B] of class bit masks.  Asynchronous."""
+    import torch
+    L = _lib.load()
+    assert gt.is_cuda and gt.is_contiguous() and gt.dim() == 3 and gt.dtype in (torch.uint8, torch.int32)
+    masks = torch.empty(gt.shape[0], dtype=torch.int32, device=gt.device)
+    flags = torch.empty(1, dtype=torch.int32, device=gt.device)
+    _lib.check(L.weaklabel_label_set_device(gt.data_ptr(), int(gt.dtype == torch.int32), int(gt.shape[0]), int(gt.shape[1]),
+                                            int(gt.shape[2]), int(H), int(W), int(num_classes), masks.data_ptr(),
+                                            flags.data_ptr(), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return masks
 
 
 def softmax_ce(logits, labels, ignore_label=255, want_grad=True):

@@ -14,6 +14,7 @@
 
 #include <stdbool.h>
 #include <stddef.h>
+#include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
@@ -99,7 +100,9 @@ WL_API int weaklabel_draw_order_host(const unsigned char *present, int B, int C,
  *    histograms) for one shape on one device; prepare() fixes the label sets,
  *    the five scalars of weaklabel.cpp:7 and the class order; run() only
  *    launches kernels on `stream` (a cudaStream_t passed as void*), never
- *    synchronises, and takes raw DEVICE pointers.
+ *    synchronises, and takes raw DEVICE pointers.  prepare() does not block
+ *    either: the tables are staged in pinned memory and uploaded with one
+ *    asynchronous copy (see weaklabel_plan_prepare_async).
  *
  *    Algorithm per image (weaklabel.cpp:35-112): absent-class suppression,
  *    floored per-pixel max, num_iter x P exact order-statistic biases
@@ -119,6 +122,27 @@ WL_API int weaklabel_plan_prepare(weaklabel_plan *plan, const unsigned char *pre
                            bool suppress_others, int num_iter, float margin_others,
                            float bg, float fg, weaklabel_rng *rng);
 
+/* The same, with the table upload queued on `stream` (a cudaStream_t as void*): the host side (label-set
+ * validation, class order from rand()) runs in the caller's thread, the tables go up with ONE
+ * asynchronous copy out of a pinned double buffer.  Never blocks on the device unless it is two
+ * uploads ahead of it.  A later run() on a different stream waits for the upload through an event. */
+WL_API int weaklabel_plan_prepare_async(weaklabel_plan *plan, const unsigned char *present,
+                                 bool suppress_others, int num_iter, float margin_others,
+                                 float bg, float fg, weaklabel_rng *rng, void *stream);
+
+/* Ground-truth shrink + label sets ON THE DEVICE (deeplab.py:110 resize_nearest_neighbor to the score
+ * size, then weaklabel.cpp:19-31): d_gt is a dense [B][Hg][Wg] DEVICE map, uint8 (gt_is_int32 = 0) or
+ * int32 (1).  d_masks[b] gets bit c set <=> class c < C seen at an even (row, column) of the shrunk map;
+ * d_flags[0] bit 0 <=> a negative label was seen.  Asynchronous on `stream`. */
+WL_API int weaklabel_label_set_device(const void *d_gt, int gt_is_int32, int B, int Hg, int Wg, int H, int W,
+                               int C, unsigned int *d_masks, int *d_flags, void *stream);
+/* prepare() from a DEVICE ground-truth map: label sets by weaklabel_label_set_device, B + 1 words come
+ * back to the host (one small stream synchronisation: the class order is a function of every label-set
+ * size and of rand()), then weaklabel_plan_prepare_async.  No host pass over the GT map. */
+WL_API int weaklabel_plan_prepare_device_gt(weaklabel_plan *plan, const void *d_gt, int gt_is_int32, int Hg, int Wg,
+                                     bool suppress_others, int num_iter, float margin_others,
+                                     float bg, float fg, weaklabel_rng *rng, void *stream);
+
 /* d_map: const float32 scores, element (b,i,c) at d_map + b*batch_stride +
  * i*pixel_stride + c (ELEMENT strides; contiguous NHWC: H*W*C and C).
  * d_labels: uint8 [B][H*W] out.  The score map is NOT modified. */
@@ -133,6 +157,12 @@ WL_API int weaklabel_estep_labels_device(weaklabel_plan *plan, const float *d_ma
 WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *plan, float *d_map,
                                         long long batch_stride, long long pixel_stride,
                                         void *stream);
+
+/* Device-side status of every run() since it was last read (read-and-clear): synchronises the plan's
+ * last stream and reads ONE int into *code (may be NULL).  0 = fine (returns WEAKLABEL_OK); 2xx / 3xx =
+ * a selection found no consistent rank -- NaN / Inf among the scores, the labels of that image are not
+ * to be trusted; 4xx = a bounded wait inside the kernel gave up (returns WEAKLABEL_ERR_CUDA). */
+WL_API int weaklabel_plan_status(weaklabel_plan *plan, int *code);
 
 /* Probes for parity tests (host copies; synchronises the plan's last stream):
  * order/bias [B][num_iter][C] indexed (iteration, visit position) with -1 / 0
@@ -184,6 +214,41 @@ WL_API int weaklabel_softmax_ce_device(const float *d_logits, const unsigned cha
                                 long long n_pix, int C, int ignore_label,
                                 float *d_loss_mean, int *d_valid, float *d_dlogits,
                                 void *d_work, void *stream);
+
+
+/* ---------------------------------------------------------------------------
+ * 7. E-step + loss as one call (deeplab.py:120-123 + 182): labels and the softmax
+ *    cross-entropy that consumes them, queued back to back on `stream`.  d_map is
+ *    the contiguous [B][H*W][C] fc8 score map (the logits); every pixel is kept
+ *    (the E-step never emits ignore_label), so the loss is a single launch.
+ *    Outputs as in weaklabel_softmax_ce_device; d_labels [B][H*W] uint8.
+ * ------------------------------------------------------------------------- */
+WL_API int weaklabel_estep_ce_device(weaklabel_plan *plan, const float *d_map, unsigned char *d_labels,
+                              float *d_loss_mean, int *d_valid, float *d_dlogits, void *d_work,
+                              void *stream);
+
+/* ---------------------------------------------------------------------------
+ * 8. DLPack front door.  weaklabel_dltensor is the DLTensor of dlpack.h (dmlc/dlpack,
+ *    third-party; restated field by field so that no foreign header is needed).  A
+ *    DLManagedTensor begins with its DLTensor, so a pointer taken from a "dltensor"
+ *    capsule (tensor.__dlpack__()) can be passed as is.  scores: float32 [B,H,W,C] in CUDA
+ *    memory on the plan's device, class stride 1, dense rows (batch and pixel strides
+ *    free); labels: uint8 [B,H,W], contiguous.
+ * ------------------------------------------------------------------------- */
+typedef struct {
+    void *data;
+    int32_t device_type;      /* DLDevice.device_type: 2 = kDLCUDA                 */
+    int32_t device_id;
+    int32_t ndim;
+    uint8_t dtype_code;       /* DLDataType.code: 1 = uint, 2 = float               */
+    uint8_t dtype_bits;
+    uint16_t dtype_lanes;
+    int64_t *shape;
+    int64_t *strides;         /* in elements; NULL = compact row-major              */
+    uint64_t byte_offset;
+} weaklabel_dltensor;
+WL_API int weaklabel_estep_labels_dlpack(weaklabel_plan *plan, const void *dl_scores, const void *dl_labels,
+                                  void *stream);
 
 #ifdef __cplusplus
 }

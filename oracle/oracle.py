@@ -35,6 +35,18 @@ def build(force=False):
         subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
 
 
+def resize_nearest(gt, H, W):
+    """deeplab.py:110 -- tf.image.resize_nearest_neighbor(label, fc8 size), align_corners=False, restated
+    from TensorFlow's documented kernel (third-party to the reference, version unpinned: parity unpinned):
+    source row = min(floor(row * float32(Hg / H)), Hg - 1), columns alike.  gt: [B,Hg,Wg] -> [B,H,W]."""
+    gt = np.asarray(gt)
+    Hg, Wg = gt.shape[1], gt.shape[2]
+    sh, sw = np.float32(Hg) / np.float32(H), np.float32(Wg) / np.float32(W)
+    ys = np.minimum(np.floor(np.arange(H, dtype=np.float32) * sh).astype(np.int64), Hg - 1)
+    xs = np.minimum(np.floor(np.arange(W, dtype=np.float32) * sw).astype(np.int64), Wg - 1)
+    return gt[:, ys][:, :, xs]
+
+
 class Oracle:
     """C restatement; batched = B consecutive single-image calls on one RNG stream."""
 

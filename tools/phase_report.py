@@ -25,3 +25,6 @@ if t.shape[1] >= 32 and t[:, 8].any():
     sel = np.maximum(t[:, 6], 1)
     has = t[:, 6] > 0
     print("per selection (us): acquire %.1f  select %.1f  fold %.1f" % tuple((t[has, k] / sel[has] / 1e3).mean() for k in (16, 17, 18)))
+    if t[:, 27].any():
+        print("own double digest: segments %.1f (max %d)  raw chunks %.1f (max %d)  segments before the cap %.1f (max %d)" % (
+            t[:, 27].mean(), t[:, 27].max(), t[:, 28].mean(), t[:, 28].max(), t[:, 29].mean(), t[:, 29].max()))
