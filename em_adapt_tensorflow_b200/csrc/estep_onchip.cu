@@ -472,6 +472,9 @@ struct Prod {
     uint64_t pol;             // L2 evict-first policy of the score stream
 };
 
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
 __device__ __forceinline__ void prod_prefetch(const Prod &w, const float *img, int q) {
     const EStepParams &p = *w.p;
     const int cpx = p.sub_px;
@@ -496,22 +499,73 @@ __device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int 
     const uint32_t bytes = (uint32_t)((nfl - nh) * 4) & ~15u;   // aligned interior
     const int t0 = nh + (int)(bytes >> 2);                      // first float of the ragged tail
     uint64_t *bar = &w.msp()->full_bar[d];
+    // the ragged head / tail floats travel as 4-byte asynchronous copies (one cp.async group per chunk and
+    // lane): a plain load here would put a global-memory round trip on the issue path of EVERY chunk.  The
+    // stage is drained by this same warp, which waits for the group (cp.async.wait_group) beside the barrier.
     if (w.lane >= 1 && w.lane <= 3) {
         const int f = w.lane - 1;
-        if (f < nh) stage[lead + f] = __ldg(g0 + f);
+        if (f < nh) cp_async4(stage + lead + f, g0 + f);
     } else if (w.lane >= 4 && w.lane <= 6) {
         const int f = t0 + (w.lane - 4);
-        if (f < nfl) stage[lead + f] = __ldg(g0 + f);
+        if (f < nfl) cp_async4(stage + lead + f, g0 + f);
     } else if (w.lane == 7) {
         if (q + p.pf_ahead < nchunks && p.pf_ahead > 0) prod_prefetch(w, img, q + p.pf_ahead);
     }
-    __syncwarp();                                               // ragged stores before the arrival (release)
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
     if (w.lane == 0) {
         if (bytes) {
             mbar_expect_tx(bar, bytes);
             bulk_g2s_hint(stage + lead + nh, g0 + nh, bytes, bar, w.pol);
         } else {
             mbar_arrive(bar);
+        }
+    }
+}
+
+// One staged chunk of a label set of PP <= 4 classes (compile-time): the compact class planes, the floored
+// running max E0 (weaklabel.cpp:67-77) and the statistics of the tile.  The producers are bound by the
+// LATENCY of this loop (one warp per chunk; measured 1.6 us per 84-pixel chunk with 85 instructions per
+// round), not by the stream, so: no branches, running pointers instead of 64-bit address arithmetic per
+// store, and three rounds of 32 pixels in flight at a time.
+struct ProdStats { uint32_t zc0, zc1, zc2, zc3, ties; float dmx; };
+template <int PP>
+__device__ __forceinline__ void prod_chunk(const float *spx, int C, int npx, int lane, int pl0, int pl1, int pl2, int pl3,
+                                           float *o0, float *o1, float *o2, float *o3, float *oe, ProdStats &st) {
+    for (int g0 = 0; g0 < npx; g0 += 96) {
+        float v[3][4];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const float *px = spx + min(g0 + 32 * r + lane, npx - 1) * C;        // clamped: always a staged pixel
+            v[r][0] = px[pl0];
+            if (PP > 1) v[r][1] = px[pl1];
+            if (PP > 2) v[r][2] = px[pl2];
+            if (PP > 3) v[r][3] = px[pl3];
+        }
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const int g = g0 + 32 * r;
+            const bool ok = g + lane < npx;
+            const float v0 = v[r][0], v1 = PP > 1 ? v[r][1] : v0, v2 = PP > 2 ? v[r][2] : v0, v3 = PP > 3 ? v[r][3] : v0;
+            float hi = v0, lo = v0;
+            if (PP > 1) { hi = fmaxf(hi, v1); lo = fminf(lo, v1); }
+            if (PP > 2) { hi = fmaxf(hi, v2); lo = fminf(lo, v2); }
+            if (PP > 3) { hi = fmaxf(hi, v3); lo = fminf(lo, v3); }
+            const float E = fmaxf(hi, FLT_MIN);                                   // the floor (weaklabel.cpp:71)
+            if (ok) {
+                __stcg(o0 + g, v0);
+                if (PP > 1) __stcg(o1 + g, v1);
+                if (PP > 2) __stcg(o2 + g, v2);
+                if (PP > 3) __stcg(o3 + g, v3);
+                __stcg(oe + g, E);
+            }
+            const uint32_t e0 = (ok && v0 == E) ? 1u : 0u, e1 = (PP > 1 && ok && v1 == E) ? 1u : 0u;
+            const uint32_t e2 = (PP > 2 && ok && v2 == E) ? 1u : 0u, e3 = (PP > 3 && ok && v3 == E) ? 1u : 0u;
+            st.zc0 += e0;
+            if (PP > 1) st.zc1 += e1;
+            if (PP > 2) st.zc2 += e2;
+            if (PP > 3) st.zc3 += e3;
+            if (PP > 1) st.ties += (e0 + e1 + e2 + e3 >= 2u) ? 1u : 0u;
+            st.dmx = fmaxf(st.dmx, ok ? __fsub_rn(E, lo) : 0.f);
         }
     }
 }
@@ -543,10 +597,22 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         if (q < NST) prod_issue(w, img, q, nchunks);
         else if (w.lane == 0) prod_prefetch(w, img, q);
     }
+    unsigned long long t_wait = 0ull, t_all0 = 0ull;
+    const bool stamp = p.prof && w.pw == 0 && w.lane == 0 && (blockIdx.x % p.G) == 0;
+    if (stamp) t_all0 = gtimer();
     for (int q = q0; q < nchunks; q += NPW) {
         const uint32_t n = w.nbase + (uint32_t)q;
         const int d = (int)(n % NST);
+        unsigned long long tw0 = 0ull;
+        if (stamp) tw0 = gtimer();
         mbar_wait(&w.msp()->full_bar[d], (n / NST) & 1u, &p, 410);
+        // my ragged floats of this chunk have landed too
+        // (the one younger group is the chunk issued into my other stage; at the tail of the image there is none)
+        static_assert(NST / NPW == 2, "one younger cp.async group at most");
+        if (q + NPW < nchunks) asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncwarp();
+        if (stamp) t_wait += gtimer() - tw0;
         const float *stage = reinterpret_cast<const float *>(w.stagingp() + (size_t)d * STAGE_BYTES);
         const int npx = min(cpx, w.n_t - q * cpx);
         const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
@@ -586,32 +652,15 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 dmx = fmaxf(dmx, __fsub_rn(E, x));
             }
         } else if (P <= 4) {
-            for (int gt = w.lane; gt < npx; gt += 32) {
-                const float *px = stage + lead + gt * p.C;
-                const float v0 = px[pl0];
-                const float v1 = (P > 1) ? px[pl1] : v0;
-                const float v2 = (P > 2) ? px[pl2] : v0;
-                const float v3 = (P > 3) ? px[pl3] : v0;
-                float E = FLT_MIN, mn = FLT_MAX;
-                if (v0 > E) E = v0;
-                if (v0 < mn) mn = v0;
-                if (v1 > E) E = v1;
-                if (v1 < mn) mn = v1;
-                if (v2 > E) E = v2;
-                if (v2 < mn) mn = v2;
-                if (v3 > E) E = v3;
-                if (v3 < mn) mn = v3;
-                __stcg(out + gt, v0);
-                if (P > 1) __stcg(out + (size_t)p.Npad + gt, v1);
-                if (P > 2) __stcg(out + 2 * (size_t)p.Npad + gt, v2);
-                if (P > 3) __stcg(out + 3 * (size_t)p.Npad + gt, v3);
-                __stcg(e0pl + i0 + gt, E);
-                const uint32_t e0 = (v0 == E) ? 1u : 0u, e1 = (P > 1 && v1 == E) ? 1u : 0u;
-                const uint32_t e2 = (P > 2 && v2 == E) ? 1u : 0u, e3 = (P > 3 && v3 == E) ? 1u : 0u;
-                zc0 += e0; zc1 += e1; zc2 += e2; zc3 += e3;
-                ties += (e0 + e1 + e2 + e3 >= 2u) ? 1u : 0u;
-                dmx = fmaxf(dmx, __fsub_rn(E, mn));
-            }
+            ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx};
+            const float *spx = stage + lead;
+            float *o0 = out + w.lane, *oe = e0pl + i0 + w.lane;
+            float *o1 = o0 + p.Npad, *o2 = o1 + p.Npad, *o3 = o2 + p.Npad;
+            if (P == 1) prod_chunk<1>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
+            else if (P == 2) prod_chunk<2>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
+            else if (P == 3) prod_chunk<3>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
+            else prod_chunk<4>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
+            zc0 = st.zc0; zc1 = st.zc1; zc2 = st.zc2; zc3 = st.zc3; ties = st.ties; dmx = st.dmx;
         } else {
             for (int gt = w.lane; gt < npx; gt += 32) {
                 const float *px = stage + lead + gt * p.C;
@@ -635,6 +684,12 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         }
         __syncwarp();                                  // stage drained by every lane
         if (q + NST < nchunks) prod_issue(w, img, q + NST, nchunks);
+    }
+    if (stamp) {
+        unsigned long long *pr = p.prof + (size_t)b * 32;
+        pr[13] = t_wait;
+        pr[14] = gtimer() - t_all0;
+        pr[15] = (unsigned long long)((nchunks - q0 + NPW - 1) / NPW);
     }
     w.nbase += (uint32_t)nchunks;
     // my share of the tile's statistics

@@ -19,6 +19,11 @@ soak)
 tests)
   timeout -k 10 1500 python -m pytest tests -q -m gpu --timeout 300 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
   grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/pytest_gpu.log | head -40 ;;
+tapi)   # the C-ABI around the kernel
+  timeout -k 10 1200 python -m pytest tests/test_gpu_api.py -q -m gpu --timeout 600 > gpurun_out/pytest_api.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_api.log
+  grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/pytest_api.log | head -40 ;;
+lat)
+  ./tools/lat 2>&1 | tee gpurun_out/lat.txt ;;
 smoke)
   timeout 200 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -3 gpurun_out/smoke.log ;;
 bk)     # kernel-only bench + per-image phase stamps

@@ -28,3 +28,10 @@ if t.shape[1] >= 32 and t[:, 8].any():
     if t[:, 27].any():
         print("own double digest: segments %.1f (max %d)  raw chunks %.1f (max %d)  segments before the cap %.1f (max %d)" % (
             t[:, 27].mean(), t[:, 27].max(), t[:, 28].mean(), t[:, 28].max(), t[:, 29].mean(), t[:, 29].max()))
+    if t[:, 14].any():
+        print("producer warp 0 of CTA 0, per image (us): streaming %.1f, of which waiting for its stages %.1f; chunks %.0f -> %.2f us per chunk, %.2f waiting" % (
+            t[:, 14].mean() / 1e3, t[:, 13].mean() / 1e3, t[:, 15].mean(), (t[:, 14] / np.maximum(t[:, 15], 1)).mean() / 1e3,
+            (t[:, 13] / np.maximum(t[:, 15], 1)).mean() / 1e3))
+        for pp in sorted(set(P)):
+            m = P == pp
+            print("   P=%d: streaming %.1f us, waiting %.1f us" % (pp, t[m, 14].mean() / 1e3, t[m, 13].mean() / 1e3))
