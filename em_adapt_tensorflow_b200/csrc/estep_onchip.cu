@@ -42,8 +42,8 @@ namespace oc {
 constexpr int NB = 2048;                // histogram bins
 constexpr int NSB = 64;                 // super bins exchanged through the mailboxes
 constexpr int SUBB = NB / NSB;          // 32 fine bins per super bin
-constexpr int WIN_SH = 16;              // 128 bins per binade inside the window
-constexpr int WIN_BINADES = 15;
+constexpr int WIN_SH = 16;              // 128 bins per binade inside the window (256 bins over 7 binades was measured:
+constexpr int WIN_BINADES = 15;         // slower -- more ranks fall below the window and cost a second round)
 constexpr int GCAP = 1024;              // candidates gathered into every CTA
 constexpr int RCMAX = 256;              // up to here the local selection ranks by counting
 constexpr int MBW = 72;                 // mailbox words per CTA per exchange (a multiple of 4)
@@ -348,8 +348,12 @@ template <int NT_> struct Cx {
     int mru;
 };
 
+// progress words of every CTA in mapped host memory (WEAKLABEL_TRAIL=1): a debugging aid of the bring-up,
+// compiled in with -DWL_TRAIL only (the test for the pointer alone cost ~1.5 % of the issue slots)
 template <int NT_> __device__ __forceinline__ void trc(const Cx<NT_> &c, int k, uint32_t v) {
+#ifdef WL_TRAIL
     if (c.p->trail && c.tid == 0) c.p->trail[blockIdx.x * 32 + k] = v;
+#endif
 }
 template <int NT_> __device__ __forceinline__ SelScratch *sel(Cx<NT_> &c) { return reinterpret_cast<SelScratch *>(c.unip()); }
 template <int NT_> __device__ __forceinline__ SumScratch *sums(Cx<NT_> &c) { return reinterpret_cast<SumScratch *>(c.unip()); }

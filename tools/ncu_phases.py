@@ -23,7 +23,7 @@ phase = None; agg = collections.Counter(); inst = collections.Counter(); lines =
 stalls = collections.defaultdict(lambda: [0] * len(st))
 tot = 0
 for addr, key, n, k, sass, sv in recs:
-    if key and key[0].startswith("estep_v") and key[1] >= body0: phase = key[1]
+    if key and key[0].startswith("estep_onchip") and key[1] >= body0: phase = key[1]
     agg[phase] += n; inst[phase] += k; tot += n
     lines[phase][key] += n
     for j, v in enumerate(sv): stalls[phase][j] += v
@@ -31,7 +31,7 @@ print("total samples", tot)
 for ph, n in sorted(agg.items(), key=lambda kv: (kv[0] or 0)):
     if n < tot * 0.004: continue
     s = sorted(zip(stalls[ph], [h for _, h in st]), reverse=True)[:3]
-    print("%5.1f%% inst=%10d body line %s: %s   [%s]" % (100.0 * n / tot, inst[ph], ph, src.get(("estep_v4.cu", ph), "")[:60],
+    print("%5.1f%% inst=%10d body line %s: %s   [%s]" % (100.0 * n / tot, inst[ph], ph, src.get(("estep_onchip.cu", ph), "")[:60],
           ", ".join("%s %.0f%%" % (h[6:], 100.0 * v / max(n, 1)) for v, h in s)))
     for key, m in lines[ph].most_common(3):
         if m >= tot * 0.004: print("          %5.1f%%  %s:%d %s" % (100.0 * m / tot, key[0], key[1], src[key][:80]))
