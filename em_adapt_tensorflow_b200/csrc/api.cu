@@ -202,6 +202,8 @@ struct weaklabel_plan {
     int tune_G, tune_TS, tune_slots, tune_path;     // tune_path: 0 auto, 1 generic, 2 on-chip
     OnchipConfig oc; bool oc_ok; int oc_slots;      // on-chip kernel (estep_onchip.cu)
     int env_prefetch, env_flags;                    // WEAKLABEL_PREFETCH / WEAKLABEL_FLAGS, read once at creation
+    int want_sums;                                  // outputs of run(): 1 = labels + sums of every image, 0 = labels only
+    int last_sums;                                  // what the last run() produced
     unsigned long long *d_prof; bool prof_on;       // [B][32] phase time stamps
     bool geometry_ok;
     int scratch_slots;
@@ -327,6 +329,8 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
         pl->env_flags = fl ? atoi(fl) : 0;
     }
     pl->launches = 0;
+    pl->want_sums = 1;
+    pl->last_sums = 1;
     pl->last_stream = nullptr;
     pl->B = B; pl->H = H; pl->W = W; pl->C = C; pl->N = H * W;
     pl->device = device;
@@ -550,9 +554,8 @@ extern "C" WL_API int weaklabel_plan_prepare_device_gt(weaklabel_plan *pl, const
     return weaklabel_plan_prepare_async(pl, pl->present_tmp.data(), suppress_others, num_iter, margin_others, bg, fg, rng, stream);
 }
 
-extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const float *d_map,
-                                             long long batch_stride, long long pixel_stride,
-                                             unsigned char *d_labels, void *stream) {
+static int run_estep(weaklabel_plan *pl, const float *d_map, long long batch_stride, long long pixel_stride,
+                     unsigned char *d_labels, void *stream, int want_sums) {
     if (!pl || !d_map) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_labels_device: NULL argument");
     if (!pl->prepared) return fail(WEAKLABEL_ERR_STATE, "plan not prepared");
     if (pixel_stride < pl->C || (pl->B > 1 && batch_stride < (long long)(pl->N - 1) * pixel_stride + pl->C))
@@ -585,6 +588,7 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
         slots_used = pl->oc_slots;
         p.pf_ahead = pl->env_prefetch;
         p.flags = pl->env_flags;
+        p.want_sums = (want_sums || !d_labels) ? 1 : 0;
         p.trail = debug_trail();
     } else {
         p.TS = pl->TS; p.ntiles = pl->ntiles; p.L = pl->L; p.G = pl->G;
@@ -605,9 +609,22 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
     }
     CUDA_TRY(cudaEventRecord(pl->ev_run, st));
     pl->last_path = path;
+    pl->last_sums = (path == 2) ? p.want_sums : 1;      // the generic kernel always forms the sums
     pl->launches += 1;
     pl->last_stream = st;
     pl->has_run = true;
+    return WEAKLABEL_OK;
+}
+
+extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const float *d_map,
+                                             long long batch_stride, long long pixel_stride,
+                                             unsigned char *d_labels, void *stream) {
+    return run_estep(pl, d_map, batch_stride, pixel_stride, d_labels, stream, pl ? pl->want_sums : 1);
+}
+
+extern "C" WL_API int weaklabel_plan_set_outputs(weaklabel_plan *pl, int with_sums) {
+    if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
+    pl->want_sums = with_sums ? 1 : 0;
     return WEAKLABEL_OK;
 }
 
@@ -616,6 +633,9 @@ extern "C" WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *pl, fl
                                                    void *stream) {
     if (!pl || !d_map) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_finalize_map_device: NULL argument");
     if (!pl->prepared) return fail(WEAKLABEL_ERR_STATE, "plan not prepared");
+    if (!pl->last_sums)
+        return fail(WEAKLABEL_ERR_STATE, "the last run() was labels-only (weaklabel_plan_set_outputs(plan, 0)): the in-place "
+                    "map needs the re-centring sums of every image");
     CUDA_TRY(cudaSetDevice(pl->device));
     FinalizeParams f;
     memset(&f, 0, sizeof f);
@@ -991,7 +1011,7 @@ extern "C" WL_API int weaklabel_estep_ce_device(weaklabel_plan *pl, const float 
                                          void *stream) {
     if (!pl || !d_map || !d_labels || !d_work) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_ce_device: NULL argument");
     if ((((uintptr_t)d_work) & 7u)) return fail(WEAKLABEL_ERR_ARG, "misaligned work pointer");
-    int rc = weaklabel_estep_labels_device(pl, d_map, (long long)pl->N * pl->C, pl->C, d_labels, stream);
+    int rc = run_estep(pl, d_map, (long long)pl->N * pl->C, pl->C, d_labels, stream, 0);     // labels only
     if (rc) return rc;
     const long long n_pix = (long long)pl->B * pl->N;
     int n = 0;

@@ -232,17 +232,6 @@ struct alignas(16) BigDigest {              // the local digest of a tile
     DigEntry seg[BIG_SEG];
 };
 
-// CTA 0 keeps the float digest of its own tile (mean_max_0) for the end of the image, when both sums are
-// walked at the same time: the segments plus the raw terms of the chunks that must be added one by one
-// (the first tile of an image crosses most of the binades).  Ranges whose terms do not fit are read back
-// from the E0 plane in the L2 scratch.
-constexpr int OWN_TERMS = 1280;
-struct alignas(16) OwnDigest {
-    int nseg, pad0, pad1, pad2;
-    DigEntry seg[BIG_SEG];
-    float terms[OWN_TERMS];
-};
-
 struct alignas(16) Misc {
     alignas(16) uint32_t outbox[2][MBW];    // alternating with the exchanges
     double wscr_d[32];
@@ -259,7 +248,7 @@ struct alignas(16) Misc {
     uint64_t res_bar;                   // the two sums landed
     unsigned long long sumres[2];       // [0] float sum bits, [1] double sum bits
     uint32_t tmem_base;                 // tcgen05.alloc result
-    uint32_t pstat[2][NPW][8];          // producers -> compute: zero counts [0..3], largest margin [4], ties [5]
+    uint32_t pstat[2][NPW][8];          // producers -> compute: zero counts [0..3], largest margin [4], ties [5], sum of E0 [6]
     int cmd_img[2];                     // image index of the command (>= B: stop)
     double bc_d;
     uint32_t bc_u;
@@ -308,8 +297,7 @@ template <int NT_> struct Layout {
     static constexpr size_t MBOX_BYTES = 2 * MAXG * MBW * 4;
     static constexpr size_t STAGING_BYTES = (size_t)NST * STAGE_BYTES;
     static size_t total(int se_floats) {
-        return A16((size_t)se_floats * 4) + MBOX_BYTES + A16(sizeof(Misc)) + uni_bytes() + 2 * A16(sizeof(Digest)) +
-               A16(sizeof(OwnDigest)) + STAGING_BYTES;
+        return A16((size_t)se_floats * 4) + MBOX_BYTES + A16(sizeof(Misc)) + uni_bytes() + 2 * A16(sizeof(Digest)) + STAGING_BYTES;
     }
 };
 
@@ -327,17 +315,17 @@ template <int NT_> struct Cx {
     // Shared memory is addressed as (dynamic shared base + byte offset), never through pointers kept in
     // this struct: if the compiler leaves the struct in local memory, a pointer loaded back from there is
     // a GENERIC pointer and every LDS / ATOMS of the kernel degrades to a generic LD / ATOM.
-    uint32_t o_mbox, o_ms, o_uni, o_outd, o_own;
+    uint32_t o_mbox, o_ms, o_uni, o_outd;
     __device__ __forceinline__ float *sE() const { return reinterpret_cast<float *>(smem0()); }
     __device__ __forceinline__ uint32_t (*mboxp() const)[MAXG][MBW] { return reinterpret_cast<uint32_t (*)[MAXG][MBW]>(smem0() + o_mbox); }
     __device__ __forceinline__ Misc *msp() const { return reinterpret_cast<Misc *>(smem0() + o_ms); }
     __device__ __forceinline__ unsigned char *unip() const { return smem0() + o_uni; }
     __device__ __forceinline__ Digest *outdp() const { return reinterpret_cast<Digest *>(smem0() + o_outd); }     // [2]: my float and double digests (pushed to CTA 0)
-    __device__ __forceinline__ OwnDigest *ownp() const { return reinterpret_cast<OwnDigest *>(smem0() + o_own); }  // CTA 0: float digest of its own tile
     int base, n_t, TQ;    // my tile: pixels [base, base + n_t), TQ = quads that hold a pixel
     uint32_t xround;      // exchanges done (mailbox / outbox / barrier parity), identical in every CTA
     uint32_t hround;      // histogram rounds done (hist buffer parity)
     uint32_t csyncs;      // plain cluster syncs done
+    uint32_t n_e0, n_dig, n_res;   // uses of the E0 / digest / result barriers (their parity; identical in every CTA)
     uint32_t tm;          // TMEM address of my lane quarter, my warp's first column of slot 0
     // per image
     int b, P;
@@ -531,7 +519,7 @@ __device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int 
 // LATENCY of this loop (one warp per chunk; measured 1.6 us per 84-pixel chunk with 85 instructions per
 // round), not by the stream, so: no branches, running pointers instead of 64-bit address arithmetic per
 // store, and three rounds of 32 pixels in flight at a time.
-struct ProdStats { uint32_t zc0, zc1, zc2, zc3, ties; float dmx; };
+struct ProdStats { uint32_t zc0, zc1, zc2, zc3, ties; float dmx, esum; };
 template <int PP>
 __device__ __forceinline__ void prod_chunk(const float *spx, int C, int npx, int lane, int pl0, int pl1, int pl2, int pl3,
                                            float *o0, float *o1, float *o2, float *o3, float *oe, ProdStats &st) {
@@ -570,6 +558,7 @@ __device__ __forceinline__ void prod_chunk(const float *spx, int C, int npx, int
             if (PP > 3) st.zc3 += e3;
             if (PP > 1) st.ties += (e0 + e1 + e2 + e3 >= 2u) ? 1u : 0u;
             st.dmx = fmaxf(st.dmx, ok ? __fsub_rn(E, lo) : 0.f);
+            st.esum += ok ? E : 0.f;
         }
     }
 }
@@ -594,7 +583,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     float *absmax = planes + (size_t)p.C * p.Npad;
     float *e0pl = planes + (size_t)(p.C + 1) * p.Npad;
     uint32_t zc0 = 0u, zc1 = 0u, zc2 = 0u, zc3 = 0u, ties = 0u;
-    float dmx = 0.f;
+    float dmx = 0.f, esum = 0.f;        // esum: plain float sum of my E0 values (a bound of the shift needs mean E0 to ~1 %)
     const int q0 = (int)((w.pw + NPW - (w.nbase % NPW)) % NPW);   // my first chunk
     // every stage is free (the producers met after the previous image): fill the ring, warm the L2
     for (int q = q0; q < nchunks && q < max(NST, p.pf_ahead); q += NPW) {
@@ -654,9 +643,10 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 absidx[i0 + gt] = (uint8_t)((tf == amax) ? first_absent : 254);
                 zc0 += (x == E) ? 1u : 0u;
                 dmx = fmaxf(dmx, __fsub_rn(E, x));
+                esum += E;
             }
         } else if (P <= 4) {
-            ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx};
+            ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx, esum};
             const float *spx = stage + lead;
             float *o0 = out + w.lane, *oe = e0pl + i0 + w.lane;
             float *o1 = o0 + p.Npad, *o2 = o1 + p.Npad, *o3 = o2 + p.Npad;
@@ -664,7 +654,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
             else if (P == 2) prod_chunk<2>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
             else if (P == 3) prod_chunk<3>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
             else prod_chunk<4>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
-            zc0 = st.zc0; zc1 = st.zc1; zc2 = st.zc2; zc3 = st.zc3; ties = st.ties; dmx = st.dmx;
+            zc0 = st.zc0; zc1 = st.zc1; zc2 = st.zc2; zc3 = st.zc3; ties = st.ties; dmx = st.dmx; esum = st.esum;
         } else {
             for (int gt = w.lane; gt < npx; gt += 32) {
                 const float *px = stage + lead + gt * p.C;
@@ -684,6 +674,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 zc3 += (px[pl3] == E) ? 1u : 0u;
                 ties += (at >= 2u) ? 1u : 0u;
                 dmx = fmaxf(dmx, __fsub_rn(E, mn));
+                esum += E;
             }
         }
         __syncwarp();                                  // stage drained by every lane
@@ -705,10 +696,11 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         zc3 += __shfl_xor_sync(0xffffffffu, zc3, o);
         ties += __shfl_xor_sync(0xffffffffu, ties, o);
         dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
+        esum += __shfl_xor_sync(0xffffffffu, esum, o);
     }
     if (w.lane == 0) {
         uint32_t *st = w.msp()->pstat[par][w.pw];
-        st[0] = zc0; st[1] = zc1; st[2] = zc2; st[3] = zc3; st[4] = dm; st[5] = ties;
+        st[0] = zc0; st[1] = zc1; st[2] = zc2; st[3] = zc3; st[4] = dm; st[5] = ties; st[6] = __float_as_uint(esum);
     }
 }
 
@@ -973,34 +965,6 @@ __device__ __forceinline__ void compact_digest(Cx<NT_> &c, Digest *out) {
     __syncwarp();
 }
 
-// warp 0 of CTA 0: keep the local (float) digest of my tile together with the raw terms it needs
-template <int NT_>
-__device__ __forceinline__ void keep_own_digest(Cx<NT_> &c) {
-    const BigDigest *big = &sums(c)->big;
-    OwnDigest *own = c.ownp();
-    const int L = c.p->L;
-    const int n = big->nseg;
-    int used = 0;                                        // floats of own->terms in use (uniform over the warp)
-    for (int i = 0; i < n; i++) {
-        DigEntry e = big->seg[i];
-        e.cslot = -1;
-        e.nterms = 0;
-        if (e.kind == 0) {
-            const int t0 = (int)e.head * L, t1 = min(((int)e.tail + 1) * L, c.n_t);
-            const int nt = max(0, t1 - t0), room = (nt + 3) & ~3;
-            if (used + room <= OWN_TERMS) {
-                for (int j = c.lane; j < room; j += 32) own->terms[used + j] = (j < nt) ? c.sE()[t0 + j] : 0.f;
-                e.cslot = used;
-                e.nterms = nt;
-                used += room;
-            }
-        }
-        if (c.lane == 0) own->seg[i] = e;
-    }
-    if (c.lane == 0) own->nseg = n;
-    __syncwarp();
-}
-
 // add terms one by one: `get(j)` delivers term j (any lane may be asked for any j, uniformly)
 template <typename T, typename G>
 __device__ __forceinline__ T add_range(T s, int i0, int i1, int lane, G &&get) {
@@ -1064,6 +1028,61 @@ __device__ __forceinline__ T walk_digest(T s, const DigEntry *seg, int nseg, con
         }
     }
     return s;
+}
+
+// One order-exact running sum (T = float: weaklabel.cpp:69-80, T = double: :102-106) of the terms in shared
+// memory (s_E): a digest per tile, pushed to CTA 0 with one bulk copy, walked there by warp 0, the result
+// stored into every CTA.  fallback(r, j): term j of tile r, for the rare ranges of a peer's digest whose
+// terms did not travel with it.  Called by every compute thread of every CTA of the cluster.
+template <typename T, int NT_, typename FB>
+__device__ __forceinline__ T exact_sum(Cx<NT_> &c, int which, FB &&fallback) {
+    typedef fp_traits<T> F;
+    const EStepParams &p = *c.p;
+    Misc *ms = c.msp();
+    const int L = p.L;
+    double tile_total, cs;
+    const double cpre = chunk_prefix(c, &tile_total, &cs);
+    if (c.tid == 32) {
+        const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
+        uint32_t *ob = outbox(c);
+        ob[0] = (uint32_t)tb; ob[1] = (uint32_t)(tb >> 32); ob[2] = 0u; ob[3] = 0u;
+    }
+    double before = 0.0;                    // plain (double) sum of the tiles of lower rank: the binade prediction
+    {
+        const uint32_t (*box)[MBW] = exchange(c, 4);
+        for (int q = 0; q < c.rank; q++)
+            before += __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
+    }
+    if (c.rank == 0 && c.tid == 0 && c.G > 1) mbar_expect_tx(&ms->dig_bar, (uint32_t)((c.G - 1) * sizeof(Digest)));
+    if (c.tid == 32) mbar_expect_tx(&ms->res_bar, 8u);
+    build_big_digest<T, NT_>(c, cpre, cs, before);
+    if (c.rank != 0) {
+        if (c.warp == 0) {
+            compact_digest(c, &c.outdp()[which]);
+            asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // my digest writes -> visible to the copy engine
+            __syncwarp();
+            if (c.lane == 0)
+                bulk_s2peer(peer_addr(&sums(c)->inbound[c.rank][which], 0), &c.outdp()[which], (uint32_t)sizeof(Digest),
+                            peer_addr(&ms->dig_bar, 0));
+        }
+    } else if (c.warp == 0) {
+        SumScratch *ss = sums(c);
+        const BigDigest *big = &ss->big;
+        T s = walk_digest<T>((T)0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.sE(), [&](int j) { return c.sE()[j]; });
+        if (c.G > 1) mbar_wait(&ms->dig_bar, c.n_dig & 1u, &p, 406);
+        for (int r = 1; r < c.G; r++) {
+            const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
+            if (n_t_r == 0) break;
+            const Digest *d = &ss->inbound[r][which];
+            s = walk_digest<T>(s, d->seg, d->nseg, &d->cross[0][0], L, n_t_r, c.lane, nullptr, [&](int j) { return fallback(r, j); });
+        }
+        const unsigned long long bits = (unsigned long long)F::bits(s);
+        if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[which], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
+    }
+    c.n_dig++;
+    mbar_wait(&ms->res_bar, c.n_res & 1u, &p, 408);
+    c.n_res++;
+    return F::from((typename F::U)ms->sumres[which]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1466,6 +1485,32 @@ static __device__ __forceinline__ int label_exact(const EStepParams &p, uint32_t
     return bi;
 }
 
+// Two distinct positive floats lo < hi stay distinct (and ordered) after the shift s, rounded to float, for
+// EVERY s in [-sneg, +spos] if no shifted value can land in a binade whose float spacing exceeds hi - lo:
+// hi - lo >= ulp(lo) = 2^(e-23) with 2^e <= lo, and every y in [lo - sneg, hi + spos] with |y| < 2^(e+1) has
+// ulp(y) <= 2^(e-23); two reals at least one grid step apart never round to the same grid point.  (The
+// shift of the E-step is <= 0 up to the rounding of mean_max_0, so positive top scores only move towards
+// finer spacing: the exact tie a selection leaves at its pivot -- or its 1-ulp neighbour -- is decided here.)
+__device__ __forceinline__ bool pair_stays_distinct(float lo, float hi, float sneg, float spos) {
+    if (!(lo > 0.f)) return false;
+    const float top = __uint_as_float((__float_as_uint(lo) & 0x7f800000u) + 0x00800000u);   // 2^(e+1) (inf: never safe)
+    return fmaxf(fabsf(__fsub_rd(lo, sneg)), __fadd_ru(hi, spos)) < top;
+}
+
+// The largest SUPPRESSED absent score of one pixel (weaklabel.cpp:45-65) out of the original map; -inf when
+// every class is present.  For the rare pixels at which all present classes hold the same final score (every
+// selection leaves such an exact tie at its pivot): an absent class can reach the maximum only there.
+__device__ __noinline__ float absent_max(const float *px, uint32_t mask, int C, float margin) {
+    float m = FLT_MAX;
+    for (int k = 0; k < C; k++)
+        if ((mask >> k) & 1u) { const float t = px[k]; if (t < m) m = t; }
+    const float low = __fsub_rn(m, margin);
+    float a = -INFINITY;
+    for (int k = 0; k < C; k++)
+        if (!((mask >> k) & 1u)) { float v = px[k]; if (v > m) v = low; a = fmaxf(a, v); }
+    return a;
+}
+
 // Pass A -- runs while the two running sums are still being walked, i.e. WITHOUT the re-centring shift
 // (weaklabel.cpp:108-112), of which only an upper bound `ashift` on the magnitude is known.  Two final
 // scores a > b can round to the same float after the shift only if a - b is below the spacing of the
@@ -1473,7 +1518,7 @@ static __device__ __forceinline__ int label_exact(const EStepParams &p, uint32_t
 // Every pixel whose first maximum is safe against that guard gets its label now; the others are
 // returned as a bit per pixel of this thread (bit 4k + e) and decided by pass B with the exact shift.
 template <int NT_, int QPT>
-__device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float ashift, int tid_q, uint32_t tm_q) {
+__device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float ashift, float spos, int tid_q, uint32_t tm_q) {
     // (tid_q, tm_q): the thread whose quads are labelled and its tensor-memory columns -- this thread's own, or
     // those of a walking warp of CTA 0 (same lane quarter, lower columns) served by a proxy warp
     const EStepParams &p = *c.p;
@@ -1510,7 +1555,14 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
                 const float lo = r0 < r1 ? a0[e] : a1[e], hi = r0 < r1 ? a1[e] : a0[e];
                 const float guard = __fmul_ru(__fadd_ru(fmaxf(fabsf(lo), fabsf(hi)), ashift), 2.4e-7f);   // > 2^-22
                 const float d = fabsf(__fsub_rn(hi, lo));
-                const bool bad = exact_all || !(d > guard) ;                // d == 0, d <= guard, NaN
+                bool bad = exact_all || !(d > guard);                       // d <= guard, NaN
+                if (bad && d > 0.f && !exact_all) bad = !pair_stays_distinct(fminf(lo, hi), fmaxf(lo, hi), ashift, spos);
+                if (d == 0.f && !exact_all && 4 * q + e < c.n_t) {
+                    // an exact tie of the two present classes goes to the lower index whatever the shift -- unless
+                    // an absent class comes within the guard of them
+                    bad = has_absent && !(__fsub_rn(lo, absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
+                                                                   c.mask, p.C, p.margin)) > guard);
+                }
                 lab4 |= (uint32_t)(hi > lo ? hi_cls : lo_cls) << (8 * e);
                 un4 |= (bad ? 1u : 0u) << e;
             }
@@ -1542,13 +1594,17 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
                 // suppressed absent score is <= the smallest present one and can reach the maximum only then;
                 // or (one present class) the suppressed absent maximum within the guard
                 bool bad = exact_all || !(__fsub_rn(best[e], near_[e]) > guard);
-                if (has_absent && !have_abs && near_[e] == -INFINITY) bad = true;
+                if (bad && !exact_all && near_[e] < best[e]) bad = !pair_stays_distinct(near_[e], best[e], ashift, spos);
+                if (has_absent && !have_abs && near_[e] == -INFINITY && !bad && 4 * q + e < c.n_t)
+                    bad = !(__fsub_rn(best[e], absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
+                                                          c.mask, p.C, p.margin)) > guard);
                 if (have_abs && !(__fsub_rn(best[e], ava[e]) > guard)) bad = true;
                 lab4 |= (uint32_t)bi[e] << (8 * e);
                 un4 |= (bad ? 1u : 0u) << e;
             }
         }
         const int i0 = 4 * q;
+        if (i0 + 3 >= c.n_t) un4 &= (1u << (c.n_t - i0)) - 1u;      // padding pixels of the last quad are nobody's
 #pragma unroll
         for (int e = 0; e < 4; e++)
             if (i0 + e < c.n_t && !((un4 >> e) & 1u)) out[i0 + e] = (uint8_t)(lab4 >> (8 * e));
@@ -1639,13 +1695,12 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         o += LY::uni_bytes();
         c.o_outd = (uint32_t)o;
         o += 2 * LY::A16(sizeof(Digest));
-        c.o_own = (uint32_t)o;
-        o += LY::A16(sizeof(OwnDigest));
         staging = smem_raw + o;
     }
     c.xround = 0;
     c.hround = 0;
     c.csyncs = 0;
+    c.n_e0 = c.n_dig = c.n_res = 0;
     c.base = c.rank * p.TS;
     c.n_t = max(0, min(p.TS, p.N - c.base));
     c.TQ = (c.n_t + 3) >> 2;
@@ -1674,7 +1729,6 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         return;
     }
     const bool lead_thread = (c.rank == 0 && c.tid == 0);
-    const int L = p.L;
 
     for (uint32_t seq = 0;; seq++) {
         // claim the image of sequence number seq + 1 (and seq when seq == 0) for the cluster and
@@ -1751,32 +1805,28 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             uint4 *h4 = reinterpret_cast<uint4 *>(sel(c)->hist);
             for (int i = c.tid; i < 2 * NBX / 4; i += NT_) h4[i] = make_uint4(0u, 0u, 0u, 0u);
         }
-        mbar_wait(&ms->e0_bar, seq & 1u, &p, 405);
+        mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 405);
+        c.n_e0++;
         for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.sE()[i] = 0.f;      // padding pixels: E = 0
         if (prof && lead_thread) prof[1] = gtimer();
         csync<NT_>();
 
         trc(c, 0, (seq << 8) | 4u);
-        // 2. one exchange: zero counts, largest margin, ties, tile totals (prediction for mean_max_0)
-        double tile_total;
-        double cs0;
-        const double cpre0 = chunk_prefix(c, &tile_total, &cs0);
-        if (prof && lead_thread) prof[10] = gtimer();
-        if (c.tid < 6) {
+        // 2. one exchange: zero counts, largest margin, ties and the plain sum of E0 of every tile (as the
+        //    producers formed them while streaming)
+        if (c.tid < 7) {
             uint32_t v = 0u;
+            float fs = 0.f;
             for (int w = 0; w < NPW; w++) {
                 const uint32_t t = ms->pstat[seq & 1u][w][c.tid];
                 v = (c.tid == 4) ? max(v, t) : v + t;
+                fs += __uint_as_float(t);
             }
-            outbox(c)[c.tid] = v;
+            outbox(c)[c.tid] = (c.tid == 6) ? __float_as_uint(fs) : v;
         }
-        if (c.tid == 32) {
-            const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
-            outbox(c)[6] = (uint32_t)tb;
-            outbox(c)[7] = (uint32_t)(tb >> 32);
-        }
+        if (c.tid == 7) outbox(c)[7] = 0u;
         float dmax_bound;
-        double before0 = 0.0, total0 = 0.0;
+        double total0 = 0.0;                  // ~ sum of E0 over the image (float partial sums: good to ~1e-5)
         uint32_t tie_bound = 0u;
         {
             const uint32_t (*box)[MBW] = exchange(c, 8);
@@ -1784,9 +1834,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             for (int q = 0; q < c.G; q++) {
                 mx = max(mx, box[q][4]);
                 tie_bound += box[q][5];
-                const double tq = __longlong_as_double((long long)((unsigned long long)box[q][6] | ((unsigned long long)box[q][7] << 32)));
-                if (q < c.rank) before0 += tq;
-                total0 += tq;
+                total0 += (double)__uint_as_float(box[q][6]);
             }
             dmax_bound = __uint_as_float(mx);
             if (c.tid < EAGER_P && c.tid < c.P) {
@@ -1795,16 +1843,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                 ms->zlb[c.tid] = z;
             }
         }
-        if (prof && lead_thread) prof[11] = gtimer();
-        // 3. mean_max_0 (weaklabel.cpp:69-80): the digest of my tile's float running sum; CTA 0 walks its own
-        //    tile at once (no incoming state), the other tiles follow at the end of the image
-        build_big_digest<float, NT_>(c, cpre0, cs0, before0);
-        if (prof && lead_thread) prof[12] = gtimer();
-        if (c.warp == 0) {
-            if (c.rank == 0) keep_own_digest(c);       // walked at the end of the image, next to the double sum
-            else compact_digest(c, &c.outdp()[0]);
-        }
-        csync<NT_>();
+        csync<NT_>();                         // zlb
         if (prof && lead_thread) prof[2] = gtimer();
 
         trc(c, 0, (seq << 8) | 6u);
@@ -1820,6 +1859,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         }
         const uint8_t *ord = p.order + (size_t)c.b * p.num_iter * p.C;
         uint32_t nsel = 0;
+        float bias_sum = 0.f;                 // every fold lifts the running max by at most its bias: bounds mean_max_1 - mean_max_0
         for (int j = 0; j < p.num_iter; j++) {
             for (int t = 0; t < c.P; t++) {
                 const int plane = ord[j * p.C + t];
@@ -1889,6 +1929,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                             ms->zlb[c.tid] = 0u;                      // a valid lower bound without the exchange
                         }
                         dmax_bound = __fadd_rn(dmax_bound, bias);
+                        bias_sum = __fadd_ru(bias_sum, bias);
                     } else if (zeros != 0xffffffffu) {
                         if (c.tid == 0) ms->zlb[plane] = zeros;       // exact count of zero margins
                     }
@@ -1905,114 +1946,77 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (prof && lead_thread) prof[3] = gtimer();
 
         trc(c, 0, (seq << 8) | 8u);
-        // 5. mean_max_1 (weaklabel.cpp:102-106): digest of the double running sum of the final E; the
-        //    digests of both sums travel to CTA 0, whose first two warps walk them at the same time
-        double cs1;
-        const double cpre1 = chunk_prefix(c, &tile_total, &cs1);
         if (prof && lead_thread) { prof[16] = t_acq; prof[17] = t_sel; prof[18] = t_fold; prof[20] = gtimer(); }
-        if (c.tid == 32) {
-            const unsigned long long tb = (unsigned long long)__double_as_longlong(tile_total);
-            uint32_t *ob = outbox(c);
-            ob[0] = (uint32_t)tb; ob[1] = (uint32_t)(tb >> 32); ob[2] = 0u; ob[3] = 0u;
+        // 5. labels, pass A.  The re-centring shift (weaklabel.cpp:108-112) is one constant per image added to
+        //    every class: it can change an argmax only through the rounding of near-ties.  Its magnitude is
+        //    bounded WITHOUT the two order-exact sums: mean_max_1 - mean_max_0 lies in [0, sum of the biases
+        //    folded] (a fold lifts the running max by at most its bias), and the sequential float sum behind
+        //    mean_max_0 is within N * 2^-24 < 2 % of the plain one.  Every pixel whose first maximum is safe
+        //    against that bound is labelled now; NaN / overflow: no pixel is safe.
+        float ashift, spos;                   // the shift lies in [-ashift, +spos]
+        {
+            const double m0 = total0 / (double)p.N;
+            const double up = 0.0202 * fabs(m0) + 1e-30, ub = (double)bias_sum * 1.001 + up;
+            ashift = (ub == ub && ub < 3.0e38) ? __double2float_ru(ub) : INFINITY;
+            spos = (up == up && up < 3.0e38) ? __double2float_ru(up) : INFINITY;
         }
-        double before1 = 0.0, total1 = 0.0;
+        unsigned long long unsure = 0ull;
+        if (p.labels) unsure = labels_pass_a<NT_, QPT>(c, ashift, spos, c.tid, c.tm);
+        // 6. does this image need the order-exact sums at all?  Only if the caller wants them (in-place map,
+        //    probes) or a pixel was left open: one flag per CTA, one exchange.
+        {
+            const bool mine = __any_sync(0xffffffffu, unsure != 0ull);
+            if (c.lane == 0) ms->wred[c.warp][0] = mine ? 1u : 0u;
+            csync<NT_>();
+            if (c.tid == 0) {
+                uint32_t any = p.want_sums ? 1u : 0u;
+                for (int w = 0; w < NW; w++) any |= ms->wred[w][0];
+                uint32_t *ob = outbox(c);
+                ob[0] = any; ob[1] = 0u; ob[2] = 0u; ob[3] = 0u;
+            }
+        }
+        bool need_sums = false;
         {
             const uint32_t (*box)[MBW] = exchange(c, 4);
-            for (int q = 0; q < c.G; q++) {
-                const double tq = __longlong_as_double((long long)((unsigned long long)box[q][0] | ((unsigned long long)box[q][1] << 32)));
-                if (q < c.rank) before1 += tq;
-                total1 += tq;
-            }
+            for (int q = 0; q < c.G; q++) need_sums = need_sums || (box[q][0] != 0u);
         }
-        // |mean_max_0 - mean_max_1| from the plain (double) sums: the sequential float sum of N positive terms
-        // is within N * 2^-24 < 2 % of the real one, the double one within rounding -- an upper bound of the
-        // shift's magnitude for pass A of the labels (NaN / overflow: no pixel is safe)
-        float ashift;
-        {
-            const double m0 = total0 / (double)p.N, m1 = total1 / (double)p.N;
-            const double ub = fabs(m0 - m1) + 0.02 * fabs(m0) + 1e-30;
-            ashift = (ub == ub && ub < 3.0e38) ? __double2float_ru(ub) : INFINITY;
-        }
-        if (prof && lead_thread) prof[21] = gtimer();
+        if (prof && lead_thread) { prof[21] = gtimer(); prof[19] = need_sums ? 1ull : 0ull; }
         // (after this exchange no CTA of the cluster is inside a selection any more: the selection
         //  scratch of CTA 0, which the incoming digests alias, is free)
-        if (c.rank == 0 && c.tid == 0 && c.G > 1) mbar_expect_tx(&ms->dig_bar, (uint32_t)((c.G - 1) * 2 * sizeof(Digest)));
-        if (c.tid == 32) mbar_expect_tx(&ms->res_bar, 16u);
-        build_big_digest<double, NT_>(c, cpre1, cs1, before1);
-        if (prof && lead_thread) prof[22] = gtimer();
-        if (c.rank != 0) {
-            if (c.warp == 0) {
-                compact_digest(c, &c.outdp()[1]);
-                asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // my digest writes -> visible to the copy engine
-                __syncwarp();
-                if (c.lane == 0) {
-                    bulk_s2peer(peer_addr(&sums(c)->inbound[c.rank][0], 0), &c.outdp()[0], (uint32_t)(2 * sizeof(Digest)), peer_addr(&ms->dig_bar, 0));
+        float mean0 = __int_as_float(0x7fc00000);                                    // NaN: not computed for this image
+        double mean1 = __longlong_as_double(0x7ff8000000000000ll), shift = mean1;
+        if (need_sums) {
+            // 7. mean_max_1 (weaklabel.cpp:102-106): the double running sum of the final E in shared memory;
+            //    absent terms of a peer's digest come out of the peer's shared memory
+            const double sum1 = exact_sum<double, NT_>(c, 1, [&](int r, int j) {
+                return __uint_as_float(ld_peer(peer_addr(c.sE(), r) + 4u * (uint32_t)j));
+            });
+            if (prof && lead_thread) prof[22] = gtimer();
+            //    mean_max_0 (weaklabel.cpp:69-80): the float running sum of E0, which the producers left in the
+            //    L2 scratch -- the final E is dead now (every CTA has the double sum), E0 takes its place
+            csync<NT_>();
+            if (c.tid == 0) {
+                const uint32_t bytes = (uint32_t)((c.n_t + 3) & ~3) * 4u;
+                if (bytes) {
+                    asm volatile("fence.proxy.async;\n" ::: "memory");
+                    mbar_expect_tx(&ms->e0_bar, bytes);
+                    const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
+                    for (uint32_t o = 0; o < bytes; o += 32768u)
+                        bulk_g2s(reinterpret_cast<unsigned char *>(c.sE()) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
+                } else {
+                    mbar_arrive(&ms->e0_bar);
                 }
             }
-        } else if (c.warp < 2) {
-            SumScratch *ss = sums(c);
-            if (c.warp == 0) {
-                // the double sum: my own tile out of my shared memory, then the digests of the peers
-                const BigDigest *big = &ss->big;
-                double s1 = walk_digest<double>(0.0, big->seg, big->nseg, nullptr, L, c.n_t, c.lane, c.sE(),
-                                                [&](int j) { return c.sE()[j]; });
-                if (prof && lead_thread) {
-                    prof[23] = gtimer();
-                    int raw = 0;
-                    for (int i = 0; i < big->nseg; i++)
-                        if (big->seg[i].kind == 0) raw += ((int)big->seg[i].tail - (int)big->seg[i].head + 1);
-                    prof[27] = (unsigned long long)big->nseg;
-                    prof[28] = (unsigned long long)raw;
-                    prof[29] = (unsigned long long)big->total;
-                }
-                if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 406);
-                if (prof && lead_thread) prof[24] = gtimer();
-                for (int r = 1; r < c.G; r++) {
-                    const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
-                    if (n_t_r == 0) break;
-                    const Digest *d = &ss->inbound[r][1];
-                    const uint32_t remote = peer_addr(c.sE(), r);
-                    s1 = walk_digest<double>(s1, d->seg, d->nseg, &d->cross[0][0], L, n_t_r, c.lane, nullptr,
-                                             [&](int j) { return __uint_as_float(ld_peer(remote + 4u * (uint32_t)j)); });
-                }
-                const unsigned long long bits = (unsigned long long)__double_as_longlong(s1);
-                if (prof && lead_thread) prof[25] = gtimer();
-                if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[1], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
-            } else {
-                // the float sum: the digest of my own tile kept since the start of the image (raw ranges that
-                // did not fit come back from the E0 plane in the L2), then the float digests of the peers
-                const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad;
-                float s0 = walk_digest<float>(0.f, c.ownp()->seg, c.ownp()->nseg, c.ownp()->terms, L, c.n_t, c.lane, nullptr,
-                                              [&](int j) { return __ldcg(e0 + j); });
-                if (c.G > 1) mbar_wait(&ms->dig_bar, seq & 1u, &p, 407);
-                for (int r = 1; r < c.G; r++) {
-                    const int n_t_r = max(0, min(p.TS, p.N - r * p.TS));
-                    if (n_t_r == 0) break;
-                    const Digest *d = &ss->inbound[r][0];
-                    const float *e0r = e0 + (size_t)r * p.TS;                                   // E0 plane of tile r (L2)
-                    s0 = walk_digest<float>(s0, d->seg, d->nseg, &d->cross[0][0], L, n_t_r, c.lane, nullptr,
-                                            [&](int j) { return __ldcg(e0r + j); });
-                }
-                const unsigned long long bits = (unsigned long long)__float_as_uint(s0);
-                if (c.lane < c.G) st_async_u64(peer_addr(&ms->sumres[0], c.lane), bits, peer_addr(&ms->res_bar, c.lane));
-            }
+            mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 409);
+            c.n_e0++;
+            for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.sE()[i] = 0.f;
+            csync<NT_>();
+            const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad;
+            const float sum0 = exact_sum<float, NT_>(c, 0, [&](int r, int j) { return __ldcg(e0 + (size_t)r * p.TS + j); });
+            mean0 = __fdiv_rn(sum0, (float)p.N);
+            mean1 = __ddiv_rn(sum1, (double)p.N);
+            shift = __dsub_rn((double)mean0, mean1);
         }
-        // 6. labels, pass A: everything that cannot depend on the rounding of the re-centring is written
-        //    while the two walks run (the walking warps of CTA 0 follow once they are done)
-        unsigned long long unsure = 0ull, unsure_px = 0ull;
-        const bool walker = (c.rank == 0 && c.warp < 2);
-        const bool proxy = (c.rank == 0 && (c.warp == 4 || c.warp == 5));       // same lane quarter as warps 0 / 1
-        if (p.labels && !walker) {
-            unsure = labels_pass_a<NT_, QPT>(c, ashift, c.tid, c.tm);
-            if (proxy) unsure_px = labels_pass_a<NT_, QPT>(c, ashift, c.tid - 128, c.tm - (uint32_t)(4 * QPT));
-        }
-        if (prof && lead_thread) prof[26] = gtimer();
-        mbar_wait(&ms->res_bar, seq & 1u, &p, 408);
-        const float sum0 = __uint_as_float((uint32_t)ms->sumres[0]);
-        const double sum1 = __longlong_as_double((long long)ms->sumres[1]);
-        const float mean0 = __fdiv_rn(sum0, (float)p.N);
-        const double mean1 = __ddiv_rn(sum1, (double)p.N);
-        const double shift = __dsub_rn((double)mean0, mean1);
         if (lead_thread) {
             p.mean0[c.b] = mean0;
             p.mean1[c.b] = mean1;
@@ -2021,7 +2025,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (prof && lead_thread) prof[4] = gtimer();
         trc(c, 0, (seq << 8) | 9u);
         //    pass B: the few pixels that need the exact shift
-        if (p.labels && __any_sync(0xffffffffu, (unsure | unsure_px) != 0ull)) {
+        if (p.labels && __any_sync(0xffffffffu, unsure != 0ull)) {
             PassB a;
             a.p = &p; a.plist = ms->plist; a.planes = c.planes; a.absmax = c.absmax; a.absidx = c.absidx;
             a.out = p.labels + (size_t)c.b * p.N + c.base;
@@ -2031,11 +2035,6 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             a.b = c.b; a.base = c.base; a.n_t = c.n_t; a.tid = c.tid; a.P = c.P; a.first_absent = c.first_absent;
             a.nt = NT_; a.qpt = QPT; a.two_slots = n_slots(QPT) > 1 ? 1 : 0;
             labels_pass_b(a);
-            if (proxy) {
-                a.unsure = unsure_px; a.tid = c.tid - 128;
-                a.t0 -= (uint32_t)(4 * QPT); a.t1 -= (uint32_t)(4 * QPT);
-                labels_pass_b(a);
-            }
         }
         csync<NT_>();
         if (prof && lead_thread) {

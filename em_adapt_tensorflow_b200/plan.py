@@ -108,6 +108,13 @@ class EStepPlan:
         self.num_iter = int(num_iter)
         return self
 
+    def set_outputs(self, sums=True):
+        """sums=True (default): labels() also leaves mean_max_0 / mean_max_1 / shift of every image (probes(),
+        finalize_map()).  sums=False: labels only -- same labels, bit for bit, but the two order-exact sums are
+        formed only for images in which a pixel's argmax can depend on the rounding of the shift."""
+        _lib.check(self._L.weaklabel_plan_set_outputs(self.handle, int(bool(sums))))
+        return self
+
     def status(self):
         """Device-side status of the runs since the last call (0 = fine); raises WeakLabelError when a kernel
         reported NaN / Inf scores or a lost arrival.  Synchronises the plan's last stream."""

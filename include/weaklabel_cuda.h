@@ -150,6 +150,15 @@ WL_API int weaklabel_estep_labels_device(weaklabel_plan *plan, const float *d_ma
                                   long long batch_stride, long long pixel_stride,
                                   unsigned char *d_labels, void *stream);
 
+/* What run() produces.  with_sums = 1 (default): labels AND mean_max_0 / mean_max_1 / shift of every image
+ * (weaklabel.cpp:69-80, 102-110) -- needed by weaklabel_estep_finalize_map_device and the probes.
+ * with_sums = 0: labels only.  The re-centring shift is one constant per image added to every class
+ * (weaklabel.cpp:108-112), so it can change the argmax only through float rounding of near-ties; the
+ * kernel bounds its magnitude, labels every pixel that is safe against the bound, and forms the two
+ * order-exact sums only for images in which some pixel is not (rare).  The labels are bit-identical in
+ * both modes; mean0 / mean1 of the other images read NaN.  The training path (labels -> loss) uses 0. */
+WL_API int weaklabel_plan_set_outputs(weaklabel_plan *plan, int with_sums);
+
 /* The reference's in-place contract on DEVICE memory: d_map becomes the
  * bias-shifted, re-centred score map (what e_step leaves in `map`).  Must be
  * called after weaklabel_estep_labels_device on the same (unmodified) d_map;

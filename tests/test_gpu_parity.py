@@ -78,6 +78,39 @@ def test_device_api_bit_exact(name, path, golden):
     assert cases.sha1(got_map) == meta[name]["map_sha1"]
 
 
+@pytest.mark.parametrize("name", [n for n in ALL if _fast_applies(cases.CASE_BY_NAME[n]["params"])])
+def test_labels_only_mode_gives_the_same_labels(name, golden):
+    """weaklabel_plan_set_outputs(plan, 0): the two order-exact sums are formed only for images in which a
+    pixel's argmax can depend on the rounding of the re-centring shift (heavy ties, huge magnitudes ...);
+    the labels must be the reference's in every case, and images whose sums were formed carry exact ones."""
+    torch = _torch()
+    meta, _ = golden
+    f, l, p = cases.build_case(name)
+    if f.strides[2] != f.shape[3] * 4:
+        pytest.skip("padded pixel stride: generic kernel")
+    want_map, want_lab, (order_o, bias_o, m0_o, m1_o) = _oracle_run(f, l, p)
+    B, H, W, C = f.shape
+    t = torch.from_numpy(np.ascontiguousarray(f)).cuda()
+    plan = wl.EStepPlan(B, H, W, C)
+    plan.set_path("fast").set_outputs(sums=False)
+    plan.prepare(wl.label_set(l, C), p["suppress_others"], p["num_iter"], p["margin_others"], p["bg"], p["fg"], rng=wl.OrderStream(1))
+    lab = plan.labels(t)
+    torch.cuda.synchronize()
+    assert np.array_equal(lab.cpu().numpy(), want_lab)
+    assert cases.sha1(lab.cpu().numpy()) == meta[name]["labels_sha1"]
+    _, bias_g, m0_g, m1_g = plan.probes()
+    assert bias_g.tobytes() == bias_o.tobytes()
+    done = ~np.isnan(m1_g)
+    assert m0_g[done].tobytes() == m0_o[done].tobytes() and m1_g[done].tobytes() == m1_o[done].tobytes()
+    with pytest.raises(wl.WeakLabelError):
+        plan.finalize_map(t)                               # needs the sums of every image
+    plan.set_outputs(sums=True)
+    assert torch.equal(plan.labels(t), lab)
+    plan.finalize_map(t)
+    assert t.cpu().numpy().tobytes() == want_map.tobytes()
+    plan.close()
+
+
 @pytest.mark.parametrize("name", [n for n in ALL if cases.CASE_BY_NAME[n]["H"] <= 100])
 def test_legacy_e_step_bit_exact(name, golden):
     """The drop-in symbol on HOST buffers with the case's own (possibly padded) strides and the
