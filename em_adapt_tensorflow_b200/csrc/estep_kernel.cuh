@@ -63,6 +63,7 @@ struct EStepParams {
     // on-chip kernel
     int se_floats;            // floats of the running-max tile in shared memory (>= TS and >= NT * L)
     int flags;                // OC_F_* switches (A/B runs and bisection; 0 = everything on)
+    int light_ok;             // the geometry holds two planes in tensor memory: label sets of <= 2 classes take the light path
     int want_sums;            // 1: mean_max_0 / mean_max_1 / shift of EVERY image are outputs (in-place map, probes);
                               // 0: labels only -- the two order-exact sums are formed only for images in which a
                               //    pixel's argmax can depend on the rounding of the shift (NaN elsewhere)

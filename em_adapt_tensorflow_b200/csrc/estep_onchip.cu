@@ -453,6 +453,12 @@ __device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, doub
 // producers: HBM -> (L2 prefetch) -> staging ring (bulk copy) -> compact planes + E0 plane in the
 // L2 scratch, zero-margin counts, tie count and the largest possible margin of my tile
 // ---------------------------------------------------------------------------------------------
+// A LIGHT image: one or two present classes, both planes resident in tensor memory for the whole image, no
+// suppressed absent maximum to keep (that needs the whole pixel): see prod_chunk_light / plane_load_light.
+__device__ __forceinline__ bool image_is_light(const EStepParams &p, int P, int cls0) {
+    return p.light_ok && P <= 2 && !(P == 1 && P < p.C && cls0 != 0) && !(p.flags & OC_F_NO_RESIDENT);
+}
+
 struct Prod {
     const EStepParams *p;
     uint32_t o_ms, o_staging; // shared memory by offset (see Cx); NST stages shared by the producer warps
@@ -563,6 +569,31 @@ __device__ __forceinline__ void prod_chunk(const float *spx, int C, int npx, int
     }
 }
 
+// The LIGHT variant for label sets of one or two classes whose planes both stay in tensor memory: the producers
+// only de-interleave (PP loads + PP stores per pixel); E0 and the statistics are formed by the compute threads
+// while they move the planes into tensor memory (plane_load_light) -- they wait for the stream of such images
+// anyway, and the producers were the bottleneck (1.15 us per chunk with E0 and the statistics in here).
+template <int PP>
+__device__ __forceinline__ void prod_chunk_light(const float *spx, int C, int npx, int lane, int pl0, int pl1, float *o0, float *o1) {
+    for (int g0 = 0; g0 < npx; g0 += 96) {
+        float v[3][2];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const float *px = spx + min(g0 + 32 * r + lane, npx - 1) * C;
+            v[r][0] = px[pl0];
+            if (PP > 1) v[r][1] = px[pl1];
+        }
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const int g = g0 + 32 * r;
+            if (g + lane < npx) {
+                __stcg(o0 + g, v[r][0]);
+                if (PP > 1) __stcg(o1 + g, v[r][1]);
+            }
+        }
+    }
+}
+
 // one image: chunks q with (nbase + q) % NPW == pw of the CTA's tile
 __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *planes, uint8_t *absidx) {
     const EStepParams &p = *w.p;
@@ -580,6 +611,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     // so the suppressed absent maximum is kept.  A background-only image needs nothing: every absent class
     // has a higher index and a suppressed score <= the background's (weaklabel.cpp:45-65).
     const bool need_abs = (P == 1) && (P < p.C) && (pl0 != 0);
+    const bool light = image_is_light(p, P, pl0);
     float *absmax = planes + (size_t)p.C * p.Npad;
     float *e0pl = planes + (size_t)(p.C + 1) * p.Npad;
     uint32_t zc0 = 0u, zc1 = 0u, zc2 = 0u, zc3 = 0u, ties = 0u;
@@ -645,6 +677,11 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 dmx = fmaxf(dmx, __fsub_rn(E, x));
                 esum += E;
             }
+        } else if (light) {
+            const float *spx = stage + lead;
+            float *o0 = out + w.lane;
+            if (P == 1) prod_chunk_light<1>(spx, p.C, npx, w.lane, pl0, pl1, o0, o0 + p.Npad);
+            else prod_chunk_light<2>(spx, p.C, npx, w.lane, pl0, pl1, o0, o0 + p.Npad);
         } else if (P <= 4) {
             ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx, esum};
             const float *spx = stage + lead;
@@ -1422,6 +1459,68 @@ __device__ __forceinline__ void plane_load(Cx<NT_> &c, int plane, int slot) {
     }
     tm_wait_st();
 }
+// LIGHT images (image_is_light): both planes go from the L2 scratch into the two tensor-memory slots and, on
+// the way, the floored running max E0 (weaklabel.cpp:67-77) goes into shared memory and the statistics of my
+// tile are formed -- zero-margin counts per plane, exact ties, the largest margin and the plain sum of E0 --
+// exactly as the producers form them for the other images.  st: zc0, zc1, ties, dmx, esum (per thread).
+struct LightStats { uint32_t zc0, zc1, ties; float dmx, esum; };
+template <int NT_, int QPT, int PP>
+__device__ __forceinline__ void plane_load_light(Cx<NT_> &c, LightStats &st) {
+    const float *s0 = c.planes + c.base, *s1 = s0 + c.p->Npad;
+    const uint32_t t0 = slot_addr<NT_, QPT>(c, 0), t1 = slot_addr<NT_, QPT>(c, 1 % n_slots(QPT));
+    float *sE = c.sE();
+    const float4 ninf = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+    for (int k0 = 0; k0 < QPT; k0 += 3) {
+        float4 a[3], b[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const int q = (k0 + r) * NT_ + c.tid;
+            a[r] = ninf; b[r] = ninf;
+            if (k0 + r < QPT && q < c.TQ) {
+                a[r] = __ldcg(reinterpret_cast<const float4 *>(s0 + 4 * q));
+                if (PP > 1) b[r] = __ldcg(reinterpret_cast<const float4 *>(s1 + 4 * q));
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            if (k0 + r >= QPT) continue;
+            const int k = k0 + r, q = k * NT_ + c.tid;
+            float va[4] = {a[r].x, a[r].y, a[r].z, a[r].w}, vb[4] = {b[r].x, b[r].y, b[r].z, b[r].w};
+            float E[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const bool ok = q < c.TQ && 4 * q + e < c.n_t;
+                if (!ok) { va[e] = -INFINITY; vb[e] = -INFINITY; }             // padding pixels: x = -inf, E = 0
+                const float v0 = va[e], v1 = PP > 1 ? vb[e] : v0;
+                const float Ee = fmaxf(fmaxf(v0, v1), FLT_MIN);
+                E[e] = ok ? Ee : 0.f;
+                const uint32_t e0 = (ok && v0 == Ee) ? 1u : 0u, e1 = (PP > 1 && ok && v1 == Ee) ? 1u : 0u;
+                st.zc0 += e0;
+                st.zc1 += e1;
+                st.ties += e0 & e1;
+                st.dmx = fmaxf(st.dmx, ok ? __fsub_rn(Ee, fminf(v0, v1)) : 0.f);
+                st.esum += ok ? Ee : 0.f;
+            }
+            tm_st4(t0 + 4 * k, make_float4(va[0], va[1], va[2], va[3]));          // warp-collective: every lane, every k
+            if (PP > 1) tm_st4(t1 + 4 * k, make_float4(vb[0], vb[1], vb[2], vb[3]));
+            if (q < c.TQ) *reinterpret_cast<float4 *>(sE + 4 * q) = make_float4(E[0], E[1], E[2], E[3]);
+        }
+    }
+    tm_wait_st();
+}
+// E0 of a LIGHT image again (the float running sum, when it is needed after all): the planes in the scratch
+// still hold the original scores -- label sets of <= 2 classes never write a plane back
+template <int NT_, int PP>
+__device__ __forceinline__ void recompute_E0_light(Cx<NT_> &c) {
+    const float *s0 = c.planes + c.base, *s1 = s0 + c.p->Npad;
+    float *sE = c.sE();
+    for (int i = c.tid; i < c.n_t; i += NT_) {
+        const float v0 = __ldcg(s0 + i), v1 = PP > 1 ? __ldcg(s1 + i) : v0;
+        sE[i] = fmaxf(fmaxf(v0, v1), FLT_MIN);
+    }
+}
+
 template <int NT_, int QPT>
 __device__ __forceinline__ void plane_store(Cx<NT_> &c, int plane, int slot) {
     float *dst = c.planes + (size_t)plane * c.p->Npad + c.base;
@@ -1782,31 +1881,58 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (prof && lead_thread) prof[8] = gtimer();
         trc(c, 0, (seq << 8) | 3u);
         trc(c, 1, (uint32_t)c.b);
-        const int n_t4 = (c.n_t + 3) & ~3;
-        if (c.tid == 0) {
-            const uint32_t bytes = (uint32_t)n_t4 * 4u;
-            if (bytes) {
-                asm volatile("fence.proxy.async;\n" ::: "memory");   // generic accesses to s_E (previous image) first
-                mbar_expect_tx(&ms->e0_bar, bytes);
-                const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
-                for (uint32_t o = 0; o < bytes; o += 32768u)
-                    bulk_g2s(reinterpret_cast<unsigned char *>(c.sE()) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
-            } else {
-                mbar_arrive(&ms->e0_bar);
-            }
-        }
-        if (!(p.flags & OC_F_NO_RESIDENT)) {
-            plane_load<NT_, QPT>(c, 0, 0);
+        const bool light = image_is_light(p, c.P, (int)im->plist[0]);
+        LightStats lst = {0u, 0u, 0u, 0.f, 0.f};
+        if (light) {
+            // LIGHT image: the producers only de-interleaved; E0 and the statistics are formed here, on the way
+            // of the planes into tensor memory
+            if (c.P == 1) plane_load_light<NT_, QPT, 1>(c, lst);
+            else plane_load_light<NT_, QPT, 2>(c, lst);
             c.res0 = 0;
-            if (n_slots(QPT) > 1 && c.P > 1) { plane_load<NT_, QPT>(c, 1, 1); c.res1 = 1; c.mru = 1; }
+            if (c.P > 1) { c.res1 = 1; c.mru = 1; }
+        } else {
+            const int n_t4 = (c.n_t + 3) & ~3;
+            if (c.tid == 0) {
+                const uint32_t bytes = (uint32_t)n_t4 * 4u;
+                if (bytes) {
+                    asm volatile("fence.proxy.async;\n" ::: "memory");   // generic accesses to s_E (previous image) first
+                    mbar_expect_tx(&ms->e0_bar, bytes);
+                    const unsigned char *src = reinterpret_cast<const unsigned char *>(c.planes + (size_t)(p.C + 1) * p.Npad + c.base);
+                    for (uint32_t o = 0; o < bytes; o += 32768u)
+                        bulk_g2s(reinterpret_cast<unsigned char *>(c.sE()) + o, src + o, min(32768u, bytes - o), &ms->e0_bar);
+                } else {
+                    mbar_arrive(&ms->e0_bar);
+                }
+            }
+            if (!(p.flags & OC_F_NO_RESIDENT)) {
+                plane_load<NT_, QPT>(c, 0, 0);
+                c.res0 = 0;
+                if (n_slots(QPT) > 1 && c.P > 1) { plane_load<NT_, QPT>(c, 1, 1); c.res1 = 1; c.mru = 1; }
+            }
         }
         if (prof && lead_thread) prof[9] = gtimer();
         {   // both histograms start every image cleared (in CTA 0 the incoming digests of the previous image lay there)
             uint4 *h4 = reinterpret_cast<uint4 *>(sel(c)->hist);
             for (int i = c.tid; i < 2 * NBX / 4; i += NT_) h4[i] = make_uint4(0u, 0u, 0u, 0u);
         }
-        mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 405);
-        c.n_e0++;
+        if (light) {
+            // my share of the tile's statistics -> one row per warp
+            uint32_t dm = __float_as_uint(lst.dmx);
+            for (int o = 16; o; o >>= 1) {
+                lst.zc0 += __shfl_xor_sync(0xffffffffu, lst.zc0, o);
+                lst.zc1 += __shfl_xor_sync(0xffffffffu, lst.zc1, o);
+                lst.ties += __shfl_xor_sync(0xffffffffu, lst.ties, o);
+                dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
+                lst.esum += __shfl_xor_sync(0xffffffffu, lst.esum, o);
+            }
+            if (c.lane == 0) {
+                uint32_t *r = ms->wred[c.warp];
+                r[0] = lst.zc0; r[1] = lst.zc1; r[2] = 0u; r[3] = 0u; r[4] = dm; r[5] = lst.ties; r[6] = __float_as_uint(lst.esum);
+            }
+        } else {
+            mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 405);
+            c.n_e0++;
+        }
         for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.sE()[i] = 0.f;      // padding pixels: E = 0
         if (prof && lead_thread) prof[1] = gtimer();
         csync<NT_>();
@@ -1817,8 +1943,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (c.tid < 7) {
             uint32_t v = 0u;
             float fs = 0.f;
-            for (int w = 0; w < NPW; w++) {
-                const uint32_t t = ms->pstat[seq & 1u][w][c.tid];
+            const int nrow = light ? NW : NPW;          // one row per compute warp (light) or per producer warp
+            for (int w = 0; w < nrow; w++) {
+                const uint32_t t = light ? ms->wred[w][c.tid] : ms->pstat[seq & 1u][w][c.tid];
                 v = (c.tid == 4) ? max(v, t) : v + t;
                 fs += __uint_as_float(t);
             }
@@ -1995,7 +2122,10 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             //    mean_max_0 (weaklabel.cpp:69-80): the float running sum of E0, which the producers left in the
             //    L2 scratch -- the final E is dead now (every CTA has the double sum), E0 takes its place
             csync<NT_>();
-            if (c.tid == 0) {
+            if (light) {
+                if (c.P == 1) recompute_E0_light<NT_, 1>(c);
+                else recompute_E0_light<NT_, 2>(c);
+            } else if (c.tid == 0) {
                 const uint32_t bytes = (uint32_t)((c.n_t + 3) & ~3) * 4u;
                 if (bytes) {
                     asm volatile("fence.proxy.async;\n" ::: "memory");
@@ -2007,12 +2137,19 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                     mbar_arrive(&ms->e0_bar);
                 }
             }
-            mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 409);
-            c.n_e0++;
+            if (!light) {
+                mbar_wait(&ms->e0_bar, c.n_e0 & 1u, &p, 409);
+                c.n_e0++;
+            }
             for (int i = c.n_t + c.tid; i < p.se_floats; i += NT_) c.sE()[i] = 0.f;
             csync<NT_>();
             const float *e0 = c.planes + (size_t)(p.C + 1) * p.Npad;
-            const float sum0 = exact_sum<float, NT_>(c, 0, [&](int r, int j) { return __ldcg(e0 + (size_t)r * p.TS + j); });
+            const float *pl0 = c.planes, *pl1 = c.planes + (c.P > 1 ? p.Npad : 0);
+            const float sum0 = exact_sum<float, NT_>(c, 0, [&](int r, int j) {
+                const size_t i = (size_t)r * p.TS + j;
+                if (light) return fmaxf(fmaxf(__ldcg(pl0 + i), __ldcg(pl1 + i)), FLT_MIN);   // E0 was never written for it
+                return __ldcg(e0 + i);
+            });
             mean0 = __fdiv_rn(sum0, (float)p.N);
             mean1 = __ddiv_rn(sum1, (double)p.N);
             shift = __dsub_rn((double)mean0, mean1);
@@ -2078,7 +2215,9 @@ static cudaError_t launch_t(const EStepParams &p, int n_clusters, cudaStream_t s
     return cudaLaunchKernelEx(&cfg, estep_onchip_kernel<NT_, QPT>, p);
 }
 
-static cudaError_t dispatch(const EStepParams &p, int qpt, int n_clusters, cudaStream_t stream, int *maxc) {
+static cudaError_t dispatch(const EStepParams &p0, int qpt, int n_clusters, cudaStream_t stream, int *maxc) {
+    EStepParams p = p0;
+    p.light_ok = n_slots(qpt) > 1 ? 1 : 0;
     if (qpt == 1) return launch_t<OC_NT, 1>(p, n_clusters, stream, maxc);
     if (qpt == 3) return launch_t<OC_NT, 3>(p, n_clusters, stream, maxc);
     if (qpt == 9) return launch_t<OC_NT, 9>(p, n_clusters, stream, maxc);
