@@ -27,12 +27,12 @@ lat)
 smoke)
   timeout 200 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -3 gpurun_out/smoke.log ;;
 bk)     # kernel-only bench + per-image phase stamps
-  timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu --no-e2e --phase-profile gpurun_out/phase.npy \
+  timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu --no-e2e --no-legs --phase-profile gpurun_out/phase.npy \
      > gpurun_out/bench_k.json 2> gpurun_out/bench_k.err; echo "bench exit $?"; cat gpurun_out/bench_k.json; tail -3 gpurun_out/bench_k.err
   python tools/phase_report.py gpurun_out/phase.npy 2>&1 | tee gpurun_out/phase.txt ;;
 ab)     # switches of the kernel, one bench line each: AB="1 2 4" bash tools/gpu.sh ab
   for fl in ${AB:-1 2 4 8 16 32}; do
-    WEAKLABEL_FLAGS=$fl timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu --no-e2e --parity-images 2 \
+    WEAKLABEL_FLAGS=$fl timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu --no-e2e --no-legs --parity-images 2 \
        --phase-profile gpurun_out/phase_f$fl.npy > gpurun_out/bench_f$fl.json 2> gpurun_out/bench_f$fl.err
     echo "flags $fl exit $?: $(python -c "import json;d=json.load(open('gpurun_out/bench_f$fl.json'));print(d['ms_per_step'], d['roofline']['frac'])" 2>&1)"
     python tools/phase_report.py gpurun_out/phase_f$fl.npy 2>&1 | tail -4
@@ -42,14 +42,14 @@ bench)
 benchref)
   timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "benchref exit $?"; cat gpurun_out/bench_ref.json ;;
 launches)
-  timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --parity-images 0 > gpurun_out/plain.log 2>&1 &&
+  timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --no-legs --parity-images 0 > gpurun_out/plain.log 2>&1 &&
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv \
-      python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --parity-images 0 > gpurun_out/ncu_launches.log 2>&1
+      python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --no-legs --parity-images 0 > gpurun_out/ncu_launches.log 2>&1
   echo "launches exit $?"; tail -12 gpurun_out/launches.csv ;;
 full)
-  timeout 600 python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 > gpurun_out/plain_full.log 2>&1 &&
+  timeout 600 python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --no-legs --parity-images 0 > gpurun_out/plain_full.log 2>&1 &&
   timeout 1200 ncu --set full --clock-control none --import-source on -k regex:estep -s 3 -c 1 -f -o gpurun_out/prof \
-      python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --parity-images 0 > gpurun_out/ncu_full.log 2>&1
+      python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --no-legs --parity-images 0 > gpurun_out/ncu_full.log 2>&1
   echo "full exit $?"; tail -3 gpurun_out/ncu_full.log ;;
 *)  echo "unknown step $what" ;;
 esac
