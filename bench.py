@@ -441,11 +441,9 @@ def main():
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
-        # NCCL's INFO log (rank / ring set-up: the driver counts ranks there) goes to a file per rank, never
-        # to stdout: rank 0 prints ONE JSON line
-        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
-        os.environ.setdefault("NCCL_DEBUG_FILE", os.path.join(ROOT, "gpurun_out", "nccl_n%d_%%h_%%p.log" % world))
+        # NCCL's log (version banner, the INFO lines the driver counts ranks in when it sets NCCL_DEBUG) goes to
+        # stderr, never to stdout: rank 0 prints ONE JSON line there.  The driver's own settings win.
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
 

@@ -22,6 +22,19 @@ tests)
 tapi)   # the C-ABI around the kernel
   timeout -k 10 1200 python -m pytest tests/test_gpu_api.py -q -m gpu --timeout 600 > gpurun_out/pytest_api.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_api.log
   grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/pytest_api.log | head -40 ;;
+c5)     # BASELINE.json configs[4]: the end-to-end EM-Adapt step, device loss vs the py_func round trip
+  timeout 900 python tools/config5.py --steps 10 --warmup 3 > gpurun_out/config5_n1.json 2> gpurun_out/config5_n1.err
+  echo "config5 exit $?"; cat gpurun_out/config5_n1.json; tail -3 gpurun_out/config5_n1.err
+  timeout 900 python tools/config5.py --steps 10 --warmup 3 --tf32 > gpurun_out/config5_n1_tf32.json 2>> gpurun_out/config5_n1.err
+  echo "config5 tf32 exit $?"; cat gpurun_out/config5_n1_tf32.json ;;
+c5n)    # the same under DDP/NCCL on NG GPUs: NG=8 bash tools/gpu.sh c5n
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NG:-2} --master-addr 127.0.0.1 --master-port 29531 \
+      tools/config5.py --steps 10 --warmup 3 > gpurun_out/config5_n${NG:-2}.json 2> gpurun_out/config5_n${NG:-2}.err
+  echo "config5 x${NG:-2} exit $?"; cat gpurun_out/config5_n${NG:-2}.json; tail -3 gpurun_out/config5_n${NG:-2}.err ;;
+benchn) # the bench under torchrun on NG GPUs, as the driver launches it
+  timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NG:-2} --master-addr 127.0.0.1 --master-port 29533 \
+      bench.py --gpus ${NG:-2} > gpurun_out/bench_n${NG:-2}.json 2> gpurun_out/bench_n${NG:-2}.err
+  echo "bench x${NG:-2} exit $?"; cat gpurun_out/bench_n${NG:-2}.json; tail -3 gpurun_out/bench_n${NG:-2}.err ;;
 lat)
   ./tools/lat 2>&1 | tee gpurun_out/lat.txt ;;
 smoke)
