@@ -48,6 +48,7 @@ ALG_BYTES_PER_PIXEL = 85          # 21*4 read + 1 label byte
 CE_BYTES_PER_PIXEL = 169          # 84 read + 84 gradient written + 1 label byte
 MAP_BYTES_PER_PIXEL = 168         # in-place map: 84 read + 84 written
 METRIC = "E-step Gpixel/s (21-class, 513^2, B200) and % of HBM roofline"
+REAL_STDOUT = None
 
 
 # ------------------------------------------------------------------------------------------
@@ -249,7 +250,7 @@ def run_reference_arm(args, rank):
                                   sample=sample),
                 e2e=dict(value=val, unit="Gpixel/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=REAL_STDOUT or sys.stdout, flush=True)
     return 0
 
 
@@ -408,11 +409,18 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries ONE JSON line: whatever a library prints there (NCCL's version banner / INFO log) is sent to
+    # stderr instead -- fd 1 is re-pointed at fd 2 and the line goes out through a private copy of the real stdout
+    global REAL_STDOUT
+    if REAL_STDOUT is None:
+        sys.stdout.flush()
+        REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
     if args.gpus > 1 and world == 1:
         # convenience: re-launch under torchrun exactly as the driver would
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
-        return subprocess.call(cmd)
+        return subprocess.call(cmd, stdout=REAL_STDOUT)
 
     if args.impl == "reference":
         return run_reference_arm(args, rank)
@@ -441,9 +449,6 @@ def main():
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
-        # NCCL's log (version banner, the INFO lines the driver counts ranks in when it sets NCCL_DEBUG) goes to
-        # stderr, never to stdout: rank 0 prints ONE JSON line there.  The driver's own settings win.
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
 
@@ -619,7 +624,7 @@ def main():
                                  note="prepare() = label-set validation + class order from rand() on the host + one "
                                       "asynchronous table upload; it overlaps the previous step's kernel"),
                     per_rank=per_rank, legs=legs)
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=REAL_STDOUT or sys.stdout, flush=True)
     if dist is not None:
         dist.destroy_process_group()
     return 0

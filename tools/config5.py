@@ -89,8 +89,10 @@ def main():
     torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = bool(args.tf32)
     torch.backends.cudnn.benchmark = True
     import torch.distributed as dist
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")      # stdout carries one JSON line: library chatter (NCCL) goes to stderr
+    os.dup2(2, 1)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries one JSON line
         dist.init_process_group("nccl", device_id=dev)
     import cases
     import em_adapt_tensorflow_b200 as wl
@@ -166,7 +168,7 @@ def main():
         if "device" in out and "pyfunc" in out:
             line["step_speedup_device_over_pyfunc"] = out["pyfunc"]["ms_per_step"] / out["device"]["ms_per_step"]
             line["loss_speedup_device_over_pyfunc"] = out["pyfunc"]["loss_fwd_bwd_ms"] / out["device"]["loss_fwd_bwd_ms"]
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
