@@ -322,8 +322,15 @@ def extra_legs(wl, torch, dev, fmap, labels, plan, peak):
     plan.set_outputs(sums=False)
     legs["finalize_map_513x256"] = dict(ms=ms, gbs=npx * MAP_BYTES_PER_PIXEL / ms / 1e6,
                                         frac=npx * MAP_BYTES_PER_PIXEL / ms / 1e6 / peak,
-                                        alg_bytes_per_pixel=MAP_BYTES_PER_PIXEL, kernels="finalize_map_kernel")
+                                        alg_bytes_per_pixel=MAP_BYTES_PER_PIXEL, kernels="finalize_tile_kernel")
     del fcopy
+    # -- EM-Fixed labels (fixed biases, no selection chain): a pure 85 B/pixel stream
+    sets_b = label_sets(B)
+    masks = torch.tensor([sum(1 << k for k in sset) for sset in sets_b], dtype=torch.int32, device=dev)
+    ms = timed(lambda: wl.fixed_bias_labels(fmap, masks, 0.5, -0.25), 5, torch)
+    legs["em_fixed_labels_513x256"] = dict(ms=ms, gpixel_s=npx / ms / 1e6, gbs=npx * ALG_BYTES_PER_PIXEL / ms / 1e6,
+                                           frac=npx * ALG_BYTES_PER_PIXEL / ms / 1e6 / peak, alg_bytes_per_pixel=ALG_BYTES_PER_PIXEL,
+                                           kernels="fixed_bias_tile_kernel")
     # -- worst-case label sets at 513^2: quotas that add up to the whole image (P = 4: every step selects), P = 21
     for name, sset, nimg in (("worst_P4_513", [0, 3, 8, 15], 60), ("worst_P21_513", list(range(21)), 30)):
         nimg = min(nimg, B)

@@ -19,7 +19,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libweaklabel_cuda.so")
-SOURCES = ["estep_kernel.cu", "estep_onchip.cu", "softmax_ce.cu", "label_set.cu", "api.cu"]
+SOURCES = ["estep_kernel.cu", "estep_onchip.cu", "softmax_ce.cu", "label_set.cu", "stream_kernels.cu", "api.cu"]
 HEADERS = ["estep_kernel.cuh", "estep_device.cuh", "seqsum.cuh", "bulk_tile.cuh", os.path.join(ROOT, "include", "weaklabel_cuda.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--fmad=false",

@@ -645,7 +645,8 @@ extern "C" WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *pl, fl
     f.shift = pl->d_shift;
     if (pl->has_run && pl->last_stream != (cudaStream_t)stream)        // biases / shift come from run()'s stream
         CUDA_TRY(cudaStreamWaitEvent((cudaStream_t)stream, pl->ev_run, 0));
-    CUDA_TRY(launch_finalize_map(f, (cudaStream_t)stream));
+    if (finalize_tiles_applicable(f) && !getenv("WEAKLABEL_FINALIZE_SIMPLE")) CUDA_TRY(launch_finalize_tiles(f, pl->sms, (cudaStream_t)stream));
+    else CUDA_TRY(launch_finalize_map(f, (cudaStream_t)stream));
     CUDA_TRY(cudaEventRecord(pl->ev_run, (cudaStream_t)stream));
     pl->launches += 1;
     pl->last_stream = (cudaStream_t)stream;
@@ -1019,6 +1020,22 @@ extern "C" WL_API int weaklabel_estep_ce_device(weaklabel_plan *pl, const float 
                                pl->sms, (cudaStream_t)stream, &n));
     pl->launches += n;
     CUDA_TRY(cudaEventRecord(pl->ev_run, (cudaStream_t)stream));
+    return WEAKLABEL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// EM-Fixed (the fixed-bias variant of the paper the reference's readme cites)
+// ---------------------------------------------------------------------------------------------
+extern "C" WL_API int weaklabel_fixed_bias_labels_device(const float *d_map, int B, int H, int W, int C,
+                                                  const unsigned int *d_masks, float bias_bg, float bias_fg,
+                                                  const unsigned char *d_strong, unsigned char *d_labels, void *stream) {
+    if (!d_map || !d_masks || !d_labels) return fail(WEAKLABEL_ERR_ARG, "weaklabel_fixed_bias_labels_device: NULL argument");
+    if (B <= 0 || H <= 0 || W <= 0 || C <= 0 || C > WEAKLABEL_MAX_CLASSES) return fail(WEAKLABEL_ERR_ARG, "bad shape");
+    if (((uintptr_t)d_map) & 3u) return fail(WEAKLABEL_ERR_ARG, "misaligned pointer");
+    if (weaklabel_device_count() <= 0)
+        return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
+    CUDA_TRY(launch_fixed_bias(d_map, (long long)B * H * W, H * W, C, d_masks, bias_bg, bias_fg, d_strong, d_labels, device_sms(),
+                               (cudaStream_t)stream));
     return WEAKLABEL_OK;
 }
 

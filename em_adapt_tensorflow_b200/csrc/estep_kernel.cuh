@@ -102,6 +102,12 @@ struct FinalizeParams {
     const double *shift;      // [B]
 };
 cudaError_t launch_finalize_map(const FinalizeParams &p, cudaStream_t stream);
+// the same on bulk tiles (stream_kernels.cu): contiguous batches of images with >= 256 pixels
+bool finalize_tiles_applicable(const FinalizeParams &p);
+cudaError_t launch_finalize_tiles(const FinalizeParams &p, int sms, cudaStream_t stream);
+// EM-Fixed labels (stream_kernels.cu): argmax over the present classes of score + fixed bias, strong labels override
+cudaError_t launch_fixed_bias(const float *map, long long n_pix, int N, int C, const uint32_t *masks, float bias_bg, float bias_fg,
+                              const uint8_t *strong, uint8_t *labels, int sms, cudaStream_t stream);
 
 // valid_known >= 0: the number of kept pixels is known (E-step labels never carry ignore_label): no count
 // pass, a single launch; < 0: counted from the labels first.  work: 16 bytes of device scratch.

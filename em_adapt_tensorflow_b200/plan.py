@@ -220,6 +220,24 @@ def label_set_device(gt, H, W, num_classes):
     return masks
 
 
+def fixed_bias_labels(fmap, masks, bias_bg, bias_fg, strong=None):
+    """EM-Fixed (the paper's fixed-bias E-step; not in the reference): label = first maximum over the present
+    classes of score + bias_bg (class 0) / bias_fg, overridden by `strong` (uint8 [B,H,W], 255 = none) where it
+    names a class.  fmap CUDA float32 [B,H,W,C] contiguous, masks int32 CUDA [B] (label_set_device)."""
+    import torch
+    L = _lib.load()
+    assert fmap.is_cuda and fmap.dtype == torch.float32 and fmap.is_contiguous() and fmap.dim() == 4
+    B, H, W, Cc = fmap.shape
+    assert masks.is_cuda and masks.dtype == torch.int32 and masks.numel() == B
+    out = torch.empty((B, H, W), dtype=torch.uint8, device=fmap.device)
+    if strong is not None:
+        assert strong.is_cuda and strong.dtype == torch.uint8 and strong.is_contiguous() and strong.numel() == B * H * W
+    _lib.check(L.weaklabel_fixed_bias_labels_device(fmap.data_ptr(), B, H, W, Cc, masks.data_ptr(), float(bias_bg), float(bias_fg),
+                                                    strong.data_ptr() if strong is not None else None, out.data_ptr(),
+                                                    C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
 def softmax_ce(logits, labels, ignore_label=255, want_grad=True):
     """Fused softmax-CE forward(+backward) with ignore_label (deeplab.py:182, network.py:77-89).
     logits CUDA float32 [..., C] contiguous, labels CUDA uint8 [...].

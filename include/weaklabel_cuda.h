@@ -237,6 +237,19 @@ WL_API int weaklabel_estep_ce_device(weaklabel_plan *plan, const float *d_map, u
                               void *stream);
 
 /* ---------------------------------------------------------------------------
+ * 7b. EM-Fixed labels -- the fixed-bias variant of the paper the reference's readme
+ *    cites (readme.md:3; NOT implemented in the reference, so there is no parity
+ *    target: the test restates it in NumPy).  label = the first maximum over the PRESENT
+ *    classes (d_masks[b], as weaklabel_label_set_device writes them) of score + bias_bg
+ *    (class 0) / bias_fg (others); an image without any present class gets 255; where
+ *    d_strong (uint8 [B][H*W], may be NULL) holds a class < C -- a pixel-level annotation of
+ *    a strongly labelled image -- that class is the label.  d_map contiguous [B][H*W][C].
+ * ------------------------------------------------------------------------- */
+WL_API int weaklabel_fixed_bias_labels_device(const float *d_map, int B, int H, int W, int C,
+                                       const unsigned int *d_masks, float bias_bg, float bias_fg,
+                                       const unsigned char *d_strong, unsigned char *d_labels, void *stream);
+
+/* ---------------------------------------------------------------------------
  * 8. DLPack front door.  weaklabel_dltensor is the DLTensor of dlpack.h (dmlc/dlpack,
  *    third-party; restated field by field so that no foreign header is needed).  A
  *    DLManagedTensor begins with its DLTensor, so a pointer taken from a "dltensor"

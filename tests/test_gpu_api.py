@@ -272,3 +272,53 @@ for rel in ("libweaklabel.so", "libestep.so", "estep/libweaklabel.so", "pythonli
     assert len(lines) == 4
     for _, rel, h in lines:
         assert h == meta["p5_seq3"]["map_sha1"], rel
+
+
+@pytest.mark.parametrize("name", ["c3_321_b30", "c2_41_b30", "p5_seq3", "shape_100x37"])
+@pytest.mark.parametrize("with_strong", [False, True])
+def test_fixed_bias_labels_em_fixed(name, with_strong):
+    """EM-Fixed (the paper's fixed-bias E-step, readme.md:3; absent from the reference -- parity unpinned):
+    against a NumPy restatement: first maximum over the present classes of score + bias, strong labels win."""
+    torch = _torch()
+    f, l, p = cases.build_case(name)
+    f = np.ascontiguousarray(f)
+    B, H, W, C = f.shape
+    present = wl.label_set(l, C).astype(bool)
+    bias = np.where(np.arange(C) == 0, np.float32(0.7), np.float32(-0.3)).astype(np.float32)
+    shifted = (f + bias[None, None, None, :]).astype(np.float32)
+    shifted[~np.broadcast_to(present[:, None, None, :], f.shape)] = -np.inf
+    want = np.argmax(shifted, axis=3).astype(np.uint8)
+    strong = None
+    if with_strong:
+        rng = np.random.default_rng(3)
+        strong = np.where(rng.random((B, H, W)) < 0.3, rng.integers(0, C, (B, H, W)), 255).astype(np.uint8)
+        want = np.where(strong < C, strong, want).astype(np.uint8)
+    t = torch.from_numpy(f).cuda()
+    masks = wl.label_set_device(torch.from_numpy(np.ascontiguousarray(l)).cuda(), H, W, C)
+    got = wl.fixed_bias_labels(t, masks, 0.7, -0.3, torch.from_numpy(strong).cuda() if with_strong else None)
+    assert np.array_equal(got.cpu().numpy(), want)
+    if not with_strong:                                   # a misaligned score map takes the plain-load path: same labels
+        flat = torch.empty(f.size + 1, dtype=torch.float32, device="cuda")
+        flat[1:] = t.reshape(-1)
+        assert torch.equal(wl.fixed_bias_labels(flat[1:].view(B, H, W, C), masks, 0.7, -0.3), got)
+
+
+@pytest.mark.parametrize("name", ["c3_321_b30", "c4_513_b4", "p5_seq3", "iter9", "shape_100x37"])
+def test_finalize_map_tiles_equal_the_simple_kernel(name, monkeypatch):
+    """The in-place map on bulk tiles (stream_kernels.cu) against the one-thread-per-pixel kernel and the oracle."""
+    torch = _torch()
+    f, l, p = cases.build_case(name)
+    want, _ = _oracle(f, l, p)
+    outs = []
+    for simple in (False, True):
+        if simple:
+            monkeypatch.setenv("WEAKLABEL_FINALIZE_SIMPLE", "1")
+        t = torch.from_numpy(np.ascontiguousarray(f)).cuda()
+        plan = wl.EStepPlan(*f.shape)
+        plan.prepare(wl.label_set(l, f.shape[3]), p["suppress_others"], p["num_iter"], p["margin_others"], p["bg"], p["fg"],
+                     rng=wl.OrderStream(1))
+        plan.labels(t)
+        plan.finalize_map(t)
+        outs.append(t.cpu().numpy())
+        plan.close()
+    assert outs[0].tobytes() == want.tobytes() and outs[1].tobytes() == want.tobytes()
