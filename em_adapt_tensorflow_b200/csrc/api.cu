@@ -744,6 +744,28 @@ static int check_shape_stride(const int *shape, const int *stride, long long *s0
     return WEAKLABEL_OK;
 }
 
+// weaklabel.cpp:19-31 over a large batch: the stride-2 scan of a 256 x 513^2 int32 map is 270 MB of host
+// memory traffic in front of the pipeline -- a few threads take blocks of images each
+static int label_set_host_parallel(const int *label, int B, int H, int W, int C, unsigned char *present) {
+    const size_t per = (size_t)H * W;
+    int nt = (int)std::min<size_t>(8, (size_t)B * per / ((size_t)4 << 20));
+    if (nt <= 1) return weaklabel_label_set_host(label, B, H, W, C, present);
+    std::vector<int> rcs(nt, 0);
+    std::vector<std::string> errs(nt);
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; t++) {
+        const int b0 = (int)((long long)B * t / nt), b1 = (int)((long long)B * (t + 1) / nt);
+        th.emplace_back([=, &rcs, &errs]() {
+            rcs[t] = b1 > b0 ? weaklabel_label_set_host(label + (size_t)b0 * per, b1 - b0, H, W, C, present + (size_t)b0 * C) : 0;
+            if (rcs[t]) errs[t] = weaklabel_last_error();          // the error string is thread-local
+        });
+    }
+    for (auto &x : th) x.join();
+    for (int t = 0; t < nt; t++)
+        if (rcs[t]) return fail(rcs[t], "%s", errs[t].c_str());
+    return WEAKLABEL_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // the legacy host-pointer path (estep.py:29-31 -> weaklabel.cpp:6-7), pipelined: the batch is cut into
 // blocks of images; block k+1 goes up (H2D) while block k is worked on and block k-1 comes back (D2H),
@@ -829,7 +851,7 @@ static int legacy_impl(float *map, const int *shape, const int *stride, const in
     rc = legacy_ctx(&lc);
     if (rc) return rc;
     g_present.resize((size_t)B * C);
-    rc = weaklabel_label_set_host(label, B, H, W, C, g_present.data());
+    rc = label_set_host_parallel(label, B, H, W, C, g_present.data());
     if (rc) return rc;
     // validate every label set before a single rand() draw or copy (the reference has no partial results either)
     for (int b = 0; b < B; b++) {

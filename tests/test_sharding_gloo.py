@@ -48,3 +48,48 @@ def test_two_rank_sharding_over_gloo(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "RANK0 OK" in r.stdout and "RANK1 OK" in r.stdout
+
+
+WORKER_LOSS = r"""
+import os, sys
+sys.path.insert(0, %(root)r); sys.path.insert(0, os.path.join(%(root)r, "tests"))
+import numpy as np, torch, torch.distributed as dist
+import em_adapt_tensorflow_b200 as wl
+from em_adapt_tensorflow_b200.loss import EMAdaptLoss
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+# the DDP-style wrapper: every rank owns its criterion (own plans, own order stream); there is no collective in it,
+# and on a machine without a CUDA device it must refuse loudly instead of falling back to a CPU path
+crit = EMAdaptLoss(seed=1 + rank)
+ok = True
+try:
+    crit(torch.zeros(2, 8, 8, 21), torch.zeros(2, 8, 8, dtype=torch.uint8))
+    ok = torch.cuda.is_available()
+except (AssertionError, wl.WeakLabelError, RuntimeError):
+    pass
+# per-rank streams are independent and reproducible
+a = [wl.OrderStream(1 + rank).next() for _ in range(3)]
+got = [None] * world
+dist.all_gather_object(got, a)
+ok = ok and got[0] != got[1] and got[rank] == [wl.OrderStream(1 + rank).next() for _ in range(1)] + a[1:]
+s = wl.OrderStream(1 + rank); b = [s.next() for _ in range(3)]
+ok = ok and a[0] == b[0]
+dist.barrier(); dist.destroy_process_group()
+print("RANK%%d %%s" %% (rank, "OK" if ok else "BAD"))
+sys.exit(0 if ok else 1)
+"""
+
+
+def test_loss_wrapper_two_ranks_over_gloo(tmp_path):
+    """EMAdaptLoss under a 2-process group: no collective inside, no CPU fallback (it refuses CPU tensors)."""
+    script = tmp_path / "worker_loss.py"
+    script.write_text(WORKER_LOSS % dict(root=ROOT))
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "RANK0 OK" in r.stdout and "RANK1 OK" in r.stdout
