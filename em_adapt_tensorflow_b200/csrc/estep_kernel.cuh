@@ -87,7 +87,8 @@ int estep_max_clusters(int G);
 // sets per resident cluster), quad (float4) pixel ownership, two class planes resident in tensor memory
 constexpr int OC_NT = 896;            // compute threads per CTA
 constexpr int OC_MAXG = 9;            // largest cluster (non-portable size; 15 of them are co-resident on B200)
-constexpr int OC_PF_AHEAD = 16;       // chunks prefetched into the L2 ahead of the staging ring
+constexpr int OC_PF_AHEAD = 0;        // chunks prefetched into the L2 ahead of the staging ring: 0 = off (measured: the producers
+                                      // are bound by instruction latency, not by data; 16 ahead costs 5 % -- tools/pf_sweep.sh)
 struct OnchipConfig { int nt, qpt, G, TS, L, cpx, se_floats, max_clusters; };
 bool onchip_configure(int N, int C, int B, int sms, int tune_G, int tune_TS, OnchipConfig *out);
 cudaError_t launch_estep_onchip(const EStepParams &p, const OnchipConfig &cfg, int n_clusters, cudaStream_t stream);
