@@ -483,40 +483,97 @@ __device__ __forceinline__ void prod_prefetch(const Prod &w, const float *img, i
         asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;\n" ::"l"(lo), "r"((uint32_t)(hi - lo)), "l"(w.pol) : "memory");
 }
 
-// called by a whole warp: copy chunk q of the tile into its stage, prefetch chunk q + pf_ahead
-__device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int q, int nchunks) {
-    const EStepParams &p = *w.p;
-    const int cpx = p.sub_px;
-    const int npx = min(cpx, w.n_t - q * cpx);
-    const int nfl = npx * p.C;
-    const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
-    const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
-    const int d = (int)((w.nbase + (uint32_t)q) % NST);
-    float *stage = reinterpret_cast<float *>(w.stagingp() + (size_t)d * STAGE_BYTES);
-    const int nh = lead ? min(4 - lead, nfl) : 0;               // floats before the first aligned 16 bytes
-    const uint32_t bytes = (uint32_t)((nfl - nh) * 4) & ~15u;   // aligned interior
-    const int t0 = nh + (int)(bytes >> 2);                      // first float of the ragged tail
-    uint64_t *bar = &w.msp()->full_bar[d];
-    // the ragged head / tail floats travel as 4-byte asynchronous copies (one cp.async group per chunk and
-    // lane): a plain load here would put a global-memory round trip on the issue path of EVERY chunk.  The
-    // stage is drained by this same warp, which waits for the group (cp.async.wait_group) beside the barrier.
-    if (w.lane >= 1 && w.lane <= 3) {
-        const int f = w.lane - 1;
-        if (f < nh) cp_async4(stage + lead + f, g0 + f);
-    } else if (w.lane >= 4 && w.lane <= 6) {
-        const int f = t0 + (w.lane - 4);
-        if (f < nfl) cp_async4(stage + lead + f, g0 + f);
-    } else if (w.lane == 7) {
-        if (q + p.pf_ahead < nchunks && p.pf_ahead > 0) prod_prefetch(w, img, q + p.pf_ahead);
+// Per-image constants of the chunk loop.  The producers are bound by the instructions AROUND the payload (a
+// chunk is ~36 instructions of payload for a light image), so everything that does not change from chunk to
+// chunk is formed once per image: when a chunk is a whole number of 16-byte units (cpx * C * 4 % 16 == 0) every
+// full chunk has the same alignment, ragged head / tail and bulk size.
+struct ChunkGeom {
+    const float *gtile;       // scores of my tile's first pixel
+    int cs;                   // floats per full chunk (cpx * C)
+    int cpx, nchunks, n_t;
+    int uniform;              // every full chunk shares lead / nh / bytes / t0
+    int lead, nh, t0;
+    uint32_t bytes;
+    uint32_t stage_s, bar_s;  // shared-window addresses of stage 0 / full_bar[0]
+    uint64_t pol;
+    int pf_ahead;
+};
+__device__ __forceinline__ void chunk_shape(const ChunkGeom &g, int C, int q, int &npx, int &lead, int &nh, uint32_t &bytes, int &t0, int &nfl) {
+    if (g.uniform && (q + 1) * g.cpx <= g.n_t) {
+        npx = g.cpx; nfl = g.cs; lead = g.lead; nh = g.nh; bytes = g.bytes; t0 = g.t0;
+    } else {
+        npx = min(g.cpx, g.n_t - q * g.cpx);
+        nfl = npx * C;
+        lead = (int)(((uintptr_t)(g.gtile + (long long)q * g.cs) & 15u) >> 2);
+        nh = lead ? min(4 - lead, nfl) : 0;               // floats before the first aligned 16 bytes
+        bytes = (uint32_t)((nfl - nh) * 4) & ~15u;          // aligned interior
+        t0 = nh + (int)(bytes >> 2);                        // first float of the ragged tail
+    }
+}
+// called by a whole warp: chunk q of the tile into ring slot d (its stage and barrier)
+__device__ __forceinline__ void prod_issue2(const ChunkGeom &g, int C, int lane, int q, int d, const Prod &w, const float *img) {
+    int npx, lead, nh, t0, nfl;
+    uint32_t bytes;
+    chunk_shape(g, C, q, npx, lead, nh, bytes, t0, nfl);
+    const float *g0 = g.gtile + (long long)q * g.cs;
+    const uint32_t stage_s = g.stage_s + (uint32_t)d * STAGE_BYTES + 4u * (uint32_t)lead, bar_s = g.bar_s + 8u * (uint32_t)d;
+    // the ragged head / tail floats travel as 4-byte asynchronous copies (one cp.async group per chunk and lane:
+    // a plain load here would put a global-memory round trip on the issue path of EVERY chunk); lanes 0-2 the
+    // head, lanes 3-5 the tail.  The stage is drained by this same warp, which waits for the group.
+    {
+        const int f = lane < 3 ? lane : t0 + lane - 3;
+        const bool mine = lane < 3 ? lane < nh : (lane < 6 && f < nfl);
+        if (mine) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(stage_s + 4u * (uint32_t)f), "l"(g0 + f) : "memory");
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
-    if (w.lane == 0) {
+    if (g.pf_ahead > 0) {                                   // warp-uniform: off by default
+        if (lane == 7 && q + g.pf_ahead < g.nchunks) prod_prefetch(w, img, q + g.pf_ahead);
+    }
+    if (lane == 0) {
         if (bytes) {
-            mbar_expect_tx(bar, bytes);
-            bulk_g2s_hint(stage + lead + nh, g0 + nh, bytes, bar, w.pol);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar_s), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n"
+                         ::"r"(stage_s + 4u * (uint32_t)nh), "l"(g0 + nh), "r"(bytes), "r"(bar_s), "l"(g.pol) : "memory");
         } else {
-            mbar_arrive(bar);
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar_s) : "memory");
         }
+    }
+}
+// The chunk loop of one image for one way of draining a stage: body(px0, npx, i0) gets the staged pixels of the
+// chunk (px0 = first pixel, C floats each), their number and the tile-relative... image-relative index of the first.
+template <typename BODY>
+__device__ __forceinline__ void prod_loop(Prod &w, const ChunkGeom &g, int C, const float *img, int q0, BODY &&body) {
+    const EStepParams &p = *w.p;
+    const uint32_t full_bar0 = g.bar_s;
+    for (int q = q0; q < g.nchunks; q += NPW) {
+        const uint32_t n = w.nbase + (uint32_t)q;
+        const int d = (int)(n % NST);
+        {   // mbar_wait on full_bar[d] (bounded)
+            const uint32_t a = full_bar0 + 8u * (uint32_t)d, parity = (n / NST) & 1u;
+            uint32_t ok;
+            unsigned long long t0w = 0ull;
+            for (;;) {
+                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                             : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+                if (ok) break;
+                const unsigned long long t = gtimer();
+                if (t0w == 0ull) t0w = t;
+                else if (t - t0w > WAIT_LIMIT_NS) wait_failed(&p, 410);
+            }
+        }
+        // my ragged floats of this chunk have landed too (the one younger group is the chunk issued into my
+        // other stage; at the tail of the image there is none)
+        static_assert(NST / NPW == 2, "one younger cp.async group at most");
+        if (q + NPW < g.nchunks) asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncwarp();
+        int npx, lead, nh, t0, nfl;
+        uint32_t bytes;
+        chunk_shape(g, C, q, npx, lead, nh, bytes, t0, nfl);
+        const float *px0 = reinterpret_cast<const float *>(w.stagingp() + (size_t)d * STAGE_BYTES) + lead;
+        body(px0, npx, w.base + q * g.cpx);
+        __syncwarp();                                  // stage drained by every lane
+        if (q + NST < g.nchunks) prod_issue2(g, C, w.lane, q + NST, d, w, img);
     }
 }
 
@@ -526,6 +583,7 @@ __device__ __forceinline__ void prod_issue(const Prod &w, const float *img, int 
 // round), not by the stream, so: no branches, running pointers instead of 64-bit address arithmetic per
 // store, and three rounds of 32 pixels in flight at a time.
 struct ProdStats { uint32_t zc0, zc1, zc2, zc3, ties; float dmx, esum; };
+template <int V> struct IntTag { static constexpr int value = V; };
 template <int PP>
 __device__ __forceinline__ void prod_chunk(const float *spx, int C, int npx, int lane, int pl0, int pl1, int pl2, int pl3,
                                            float *o0, float *o1, float *o2, float *o3, float *oe, ProdStats &st) {
@@ -617,38 +675,31 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     uint32_t zc0 = 0u, zc1 = 0u, zc2 = 0u, zc3 = 0u, ties = 0u;
     float dmx = 0.f, esum = 0.f;        // esum: plain float sum of my E0 values (a bound of the shift needs mean E0 to ~1 %)
     const int q0 = (int)((w.pw + NPW - (w.nbase % NPW)) % NPW);   // my first chunk
-    // every stage is free (the producers met after the previous image): fill the ring, warm the L2
-    for (int q = q0; q < nchunks && q < max(NST, p.pf_ahead); q += NPW) {
-        if (q < NST) prod_issue(w, img, q, nchunks);
-        else if (w.lane == 0) prod_prefetch(w, img, q);
-    }
-    unsigned long long t_wait = 0ull, t_all0 = 0ull;
-    const bool stamp = p.prof && w.pw == 0 && w.lane == 0 && (blockIdx.x % p.G) == 0;
-    if (stamp) t_all0 = gtimer();
-    for (int q = q0; q < nchunks; q += NPW) {
-        const uint32_t n = w.nbase + (uint32_t)q;
-        const int d = (int)(n % NST);
-        unsigned long long tw0 = 0ull;
-        if (stamp) tw0 = gtimer();
-        mbar_wait(&w.msp()->full_bar[d], (n / NST) & 1u, &p, 410);
-        // my ragged floats of this chunk have landed too
-        // (the one younger group is the chunk issued into my other stage; at the tail of the image there is none)
-        static_assert(NST / NPW == 2, "one younger cp.async group at most");
-        if (q + NPW < nchunks) asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-        else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-        __syncwarp();
-        if (stamp) t_wait += gtimer() - tw0;
-        const float *stage = reinterpret_cast<const float *>(w.stagingp() + (size_t)d * STAGE_BYTES);
-        const int npx = min(cpx, w.n_t - q * cpx);
-        const float *g0 = img + (long long)(w.base + q * cpx) * p.C;
-        const int lead = (int)(((uintptr_t)g0 & 15u) >> 2);
-        const int i0 = w.base + q * cpx;
-        float *out = planes + i0;
-        if (need_abs) {
-            for (int gt = w.lane; gt < npx; gt += 32) {
-                const float *px = stage + lead + gt * p.C;
+    ChunkGeom g;
+    g.gtile = img + (long long)w.base * p.C;
+    g.cpx = cpx; g.cs = cpx * p.C; g.nchunks = nchunks; g.n_t = w.n_t;
+    g.uniform = ((g.cs & 3) == 0) ? 1 : 0;
+    g.lead = (int)(((uintptr_t)g.gtile & 15u) >> 2);
+    g.nh = g.lead ? min(4 - g.lead, g.cs) : 0;
+    g.bytes = (uint32_t)((g.cs - g.nh) * 4) & ~15u;
+    g.t0 = g.nh + (int)(g.bytes >> 2);
+    g.stage_s = smem_u32(w.stagingp());
+    g.bar_s = smem_u32(&w.msp()->full_bar[0]);
+    g.pol = w.pol;
+    g.pf_ahead = p.pf_ahead;
+    // every stage is free (the producers met after the previous image): fill the ring
+    for (int q = q0; q < nchunks && q < NST; q += NPW) prod_issue2(g, p.C, w.lane, q, (int)((w.nbase + (uint32_t)q) % NST), w, img);
+    const int C = p.C;
+    const int lane = w.lane;
+    const size_t npad = (size_t)p.Npad;
+    if (need_abs) {
+        const float margin = p.margin;
+        prod_loop(w, g, C, img, q0, [&](const float *px0, int npx, int i0) {
+            float *out = planes + i0;
+            for (int gt = lane; gt < npx; gt += 32) {
+                const float *px = px0 + gt * C;
                 const float x = px[pl0];
-                const float low = __fsub_rn(x, p.margin);
+                const float low = __fsub_rn(x, margin);
                 float a0 = -INFINITY, a1 = -INFINITY;
                 int k = 0;
                 for (; k + 1 < pl0; k += 2) {
@@ -658,12 +709,12 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 }
                 if (k < pl0) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
                 k = max(k, pl0 + 1);
-                for (; k + 1 < p.C; k += 2) {
+                for (; k + 1 < C; k += 2) {
                     const float t0 = px[k], t1 = px[k + 1];
                     a0 = fmaxf(a0, t0 > x ? low : t0);
                     a1 = fmaxf(a1, t1 > x ? low : t1);
                 }
-                if (k < p.C) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
+                if (k < C) { const float t0 = px[k]; a0 = fmaxf(a0, t0 > x ? low : t0); }
                 const float amax = fmaxf(a0, a1);
                 float tf = px[first_absent];
                 if (tf > x) tf = low;
@@ -677,28 +728,41 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 dmx = fmaxf(dmx, __fsub_rn(E, x));
                 esum += E;
             }
-        } else if (light) {
-            const float *spx = stage + lead;
-            float *o0 = out + w.lane;
-            if (P == 1) prod_chunk_light<1>(spx, p.C, npx, w.lane, pl0, pl1, o0, o0 + p.Npad);
-            else prod_chunk_light<2>(spx, p.C, npx, w.lane, pl0, pl1, o0, o0 + p.Npad);
-        } else if (P <= 4) {
-            ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx, esum};
-            const float *spx = stage + lead;
-            float *o0 = out + w.lane, *oe = e0pl + i0 + w.lane;
-            float *o1 = o0 + p.Npad, *o2 = o1 + p.Npad, *o3 = o2 + p.Npad;
-            if (P == 1) prod_chunk<1>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
-            else if (P == 2) prod_chunk<2>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
-            else if (P == 3) prod_chunk<3>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
-            else prod_chunk<4>(spx, p.C, npx, w.lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
-            zc0 = st.zc0; zc1 = st.zc1; zc2 = st.zc2; zc3 = st.zc3; ties = st.ties; dmx = st.dmx; esum = st.esum;
-        } else {
-            for (int gt = w.lane; gt < npx; gt += 32) {
-                const float *px = stage + lead + gt * p.C;
+        });
+    } else if (light && P == 1) {
+        prod_loop(w, g, C, img, q0, [&](const float *px0, int npx, int i0) {
+            float *o0 = planes + i0 + lane;
+            prod_chunk_light<1>(px0, C, npx, lane, pl0, pl1, o0, o0 + npad);
+        });
+    } else if (light) {
+        prod_loop(w, g, C, img, q0, [&](const float *px0, int npx, int i0) {
+            float *o0 = planes + i0 + lane;
+            prod_chunk_light<2>(px0, C, npx, lane, pl0, pl1, o0, o0 + npad);
+        });
+    } else if (P <= 4) {
+        ProdStats st = {zc0, zc1, zc2, zc3, ties, dmx, esum};
+        auto run = [&](auto tag) {
+            constexpr int PP = decltype(tag)::value;
+            prod_loop(w, g, C, img, q0, [&](const float *px0, int npx, int i0) {
+                float *o0 = planes + i0 + lane, *oe = e0pl + i0 + lane;
+                float *o1 = o0 + npad, *o2 = o1 + npad, *o3 = o2 + npad;
+                prod_chunk<PP>(px0, C, npx, lane, pl0, pl1, pl2, pl3, o0, o1, o2, o3, oe, st);
+            });
+        };
+        if (P == 1) run(IntTag<1>());
+        else if (P == 2) run(IntTag<2>());
+        else if (P == 3) run(IntTag<3>());
+        else run(IntTag<4>());
+        zc0 = st.zc0; zc1 = st.zc1; zc2 = st.zc2; zc3 = st.zc3; ties = st.ties; dmx = st.dmx; esum = st.esum;
+    } else {
+        prod_loop(w, g, C, img, q0, [&](const float *px0, int npx, int i0) {
+            float *out = planes + i0;
+            for (int gt = lane; gt < npx; gt += 32) {
+                const float *px = px0 + gt * C;
                 float E = FLT_MIN, mn = FLT_MAX;
                 for (int k = 0; k < P; k++) {
                     const float v = px[pl[k]];
-                    __stcg(out + (size_t)k * p.Npad + gt, v);
+                    __stcg(out + (size_t)k * npad + gt, v);
                     if (v > E) E = v;
                     if (v < mn) mn = v;
                 }
@@ -713,15 +777,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
                 dmx = fmaxf(dmx, __fsub_rn(E, mn));
                 esum += E;
             }
-        }
-        __syncwarp();                                  // stage drained by every lane
-        if (q + NST < nchunks) prod_issue(w, img, q + NST, nchunks);
-    }
-    if (stamp) {
-        unsigned long long *pr = p.prof + (size_t)b * 32;
-        pr[13] = t_wait;
-        pr[14] = gtimer() - t_all0;
-        pr[15] = (unsigned long long)((nchunks - q0 + NPW - 1) / NPW);
+        });
     }
     w.nbase += (uint32_t)nchunks;
     // my share of the tile's statistics
