@@ -58,6 +58,7 @@ constexpr int DIG_SEG = 8;              // segments of a pushed digest
 constexpr int DIG_CROSS = 3;            // binade-crossing chunks whose terms travel with the digest
 constexpr int DIG_L = 44;               // terms per crossing chunk (>= the longest chunk)
 constexpr int BIG_SEG = 64;             // segments of the local digest
+constexpr int ORD_S = 512;              // bytes of the order table kept in shared memory (num_iter * C <= 512, else global)
 constexpr unsigned long long WAIT_LIMIT_NS = 4000000000ull;   // a wait gives up after 4 s (status + trap instead of a hung GPU)
 static_assert(NST % NPW == 0, "a stage must always belong to the same producer warp");
 static_assert(MBW % 4 == 0 && NSB <= MBW, "mailbox rows are moved as 16-byte vectors");
@@ -262,6 +263,7 @@ struct alignas(16) Misc {
     uint32_t wfirst[32];
     uint8_t plist[MAXC];
     uint8_t pplist[NPW][MAXC];          // the producers' copy (image t+1)
+    uint8_t ord_s[ORD_S];               // class order of the image in work (a skipped step must not cost a global load)
 };
 
 constexpr int NBX = NB + 32;             // + one private zero-margin counter per warp
@@ -1930,6 +1932,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             ms->plist[c.tid] = im->plist[c.tid];
             ms->zlb[c.tid] = 0u;
         }
+        const bool ord_in_smem = p.num_iter * p.C <= ORD_S;
+        if (ord_in_smem && c.tid >= 64 && c.tid - 64 < p.num_iter * p.C)
+            ms->ord_s[c.tid - 64] = p.order[(size_t)c.b * p.num_iter * p.C + (c.tid - 64)];
         // 1. the planes of my tile are in the scratch (written by my producers together with E0, the
         //    zero-margin counts, the tie count and the largest margin): E0 -> shared memory by bulk
         //    copy, the first two planes -> tensor memory meanwhile
@@ -2040,12 +2045,12 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             for (int k = 0; k < c.P; k++) quota += (ms->plist[k] == 0) ? p.nth_bg : p.nth_fg;
             track_zeros = quota < (long long)p.N - (p.N >> 6);
         }
-        const uint8_t *ord = p.order + (size_t)c.b * p.num_iter * p.C;
+        const uint8_t *ord_g = p.order + (size_t)c.b * p.num_iter * p.C;
         uint32_t nsel = 0;
         float bias_sum = 0.f;                 // every fold lifts the running max by at most its bias: bounds mean_max_1 - mean_max_0
         for (int j = 0; j < p.num_iter; j++) {
             for (int t = 0; t < c.P; t++) {
-                const int plane = ord[j * p.C + t];
+                const int plane = ord_in_smem ? ms->ord_s[j * p.C + t] : ord_g[j * p.C + t];
                 const int cls = ms->plist[plane];
                 const uint32_t k = (uint32_t)((cls == 0) ? p.nth_bg : p.nth_fg);      // weaklabel.cpp:88
                 float bias = 0.f;
