@@ -1668,6 +1668,10 @@ __device__ __noinline__ float absent_max(const float *px, uint32_t mask, int C, 
     return a;
 }
 
+template <int NT_> __device__ __forceinline__ bool labels_via_smem(const Cx<NT_> &c) {
+    return (size_t)c.n_t + 32 <= sizeof(SelScratch);
+}
+
 // Pass A -- runs while the two running sums are still being walked, i.e. WITHOUT the re-centring shift
 // (weaklabel.cpp:108-112), of which only an upper bound `ashift` on the magnitude is known.  Two final
 // scores a > b can round to the same float after the shift only if a - b is below the spacing of the
@@ -1685,6 +1689,10 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
         for (int i = tid_q; i < c.n_t; i += NT_) out[i] = 0;
         return 0ull;
     }
+    // the tile's labels are collected in the (now idle) selection scratch, one word per quad, and leave in
+    // 16-byte stores (labels_copy_out) instead of one byte store per pixel
+    const bool via_smem = labels_via_smem<NT_>(c);
+    uint32_t *labs = reinterpret_cast<uint32_t *>(c.unip());
     const bool has_absent = c.P < p.C;
     const bool have_abs = has_absent && c.P == 1;          // suppressed absent maximum was kept
     const bool exact_all = (p.flags & OC_F_NO_FASTLABEL) != 0;
@@ -1762,12 +1770,47 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
         }
         const int i0 = 4 * q;
         if (i0 + 3 >= c.n_t) un4 &= (1u << (c.n_t - i0)) - 1u;      // padding pixels of the last quad are nobody's
+        if (via_smem) {
+            labs[q] = lab4;                     // open pixels too: pass B overwrites them in the label map
+        } else {
 #pragma unroll
-        for (int e = 0; e < 4; e++)
-            if (i0 + e < c.n_t && !((un4 >> e) & 1u)) out[i0 + e] = (uint8_t)(lab4 >> (8 * e));
+            for (int e = 0; e < 4; e++)
+                if (i0 + e < c.n_t && !((un4 >> e) & 1u)) out[i0 + e] = (uint8_t)(lab4 >> (8 * e));
+        }
         unsure |= (unsigned long long)un4 << (4 * k);
     }
     return unsure;
+}
+
+// The tile's labels, left in the selection scratch by pass A, go to the label map: the tile starts at an
+// arbitrary byte of the map (513^2 / 9 pixels per tile), so the words are re-aligned to the destination
+// with funnel shifts and leave as 16-byte stores; head and tail bytes one by one.
+template <int NT_>
+__device__ __forceinline__ void labels_copy_out(Cx<NT_> &c) {
+    const EStepParams &p = *c.p;
+    if (!labels_via_smem<NT_>(c)) return;
+    if (c.P == 1 && c.msp()->plist[0] == 0) return;              // background only: written directly
+    uint8_t *dst = p.labels + (size_t)c.b * p.N + c.base;
+    const uint32_t *S = reinterpret_cast<const uint32_t *>(c.unip());
+    const uint8_t *Sb = reinterpret_cast<const uint8_t *>(S);
+    const int n = c.n_t;
+    const int head = min(n, (int)((16u - (uint32_t)((uintptr_t)dst & 15u)) & 15u));
+    const int nvec = (n - head) >> 4;
+    if (c.tid < head) dst[c.tid] = Sb[c.tid];
+    for (int v = c.tid; v < nvec; v += NT_) {
+        const int o = head + 16 * v;
+        const uint32_t *w = S + (o >> 2);
+        const uint32_t sh = (uint32_t)(o & 3) * 8u;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = sh ? w[4] : 0u;
+        uint4 r;
+        r.x = __funnelshift_r(w0, w1, sh);
+        r.y = __funnelshift_r(w1, w2, sh);
+        r.z = __funnelshift_r(w2, w3, sh);
+        r.w = __funnelshift_r(w3, w4, sh);
+        *reinterpret_cast<uint4 *>(dst + o) = r;
+    }
+    const int t0 = head + 16 * nvec;
+    if (c.tid < n - t0) dst[t0 + c.tid] = Sb[t0 + c.tid];
 }
 
 // Pass B -- the pixels pass A left open, now with the exact shift: the reference's own arithmetic
@@ -2156,6 +2199,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
             const bool mine = __any_sync(0xffffffffu, unsure != 0ull);
             if (c.lane == 0) ms->wred[c.warp][0] = mine ? 1u : 0u;
             csync<NT_>();
+            if (p.labels) labels_copy_out<NT_>(c);
             if (c.tid == 0) {
                 uint32_t any = p.want_sums ? 1u : 0u;
                 for (int w = 0; w < NW; w++) any |= ms->wred[w][0];
