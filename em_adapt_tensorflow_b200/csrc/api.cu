@@ -1026,6 +1026,26 @@ extern "C" WL_API int weaklabel_softmax_ce_device(const float *d_logits, const u
     return WEAKLABEL_OK;
 }
 
+// The loss for callers that cannot allocate: no d_work argument, the scratch is a static device array of
+// softmax_ce.cu.  No counterpart in the reference.  Nothing on
+// this path calls cudaMalloc / cudaFree or an allocating library routine.
+extern "C" WL_API int weaklabel_softmax_ce_static(const float *d_logits, const unsigned char *d_labels,
+                                           long long n_pix, int C, int ignore_label,
+                                           float *d_loss_mean, int *d_valid, float *d_dlogits, void *stream) {
+    if (!d_logits || !d_labels) return fail(WEAKLABEL_ERR_ARG, "weaklabel_softmax_ce_static: NULL argument");
+    if (n_pix < 0 || C <= 0 || C > WEAKLABEL_MAX_CLASSES) return fail(WEAKLABEL_ERR_ARG, "bad n_pix/C");
+    if (n_pix > WEAKLABEL_CE_STATIC_MAX_PIXELS)
+        return fail(WEAKLABEL_ERR_ARG, "weaklabel_softmax_ce_static: n_pix exceeds WEAKLABEL_CE_STATIC_MAX_PIXELS (2^31 - 1: "
+                                       "the kept-pixel counter in the static scratch is 32 bits wide); split the batch");
+    if (((uintptr_t)d_logits) & 3u) return fail(WEAKLABEL_ERR_ARG, "misaligned pointer");
+    if (weaklabel_device_count() <= 0)
+        return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
+    int n = 0;
+    CUDA_TRY(launch_softmax_ce_static(d_logits, d_labels, n_pix, C, ignore_label, d_loss_mean, d_valid, d_dlogits,
+                                      device_sms(), (cudaStream_t)stream, &n));
+    return WEAKLABEL_OK;
+}
+
 // E-step labels and the loss that consumes them, queued back to back on one stream: the label map goes
 // from the E-step kernel to the loss kernel through the L2, every pixel is kept (the E-step never emits
 // ignore_label), so the loss is ONE launch with the denominator B * H * W known beforehand.

@@ -116,6 +116,12 @@ cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long l
                               int ignore_label, float *loss_mean, int *valid, float *dlogits,
                               void *work, long long valid_known, int sms, cudaStream_t stream, int *n_launches);
 
+// the same with the scratch in a file-scope device array of softmax_ce.cu (no allocation anywhere; calls on one
+// device share the array and must not overlap); the labels are counted first (valid_known = -1)
+cudaError_t launch_softmax_ce_static(const float *logits, const uint8_t *labels, long long n_pix, int C, int ignore_label,
+                                     float *loss_mean, int *valid, float *dlogits, int sms, cudaStream_t stream,
+                                     int *n_launches);
+
 // GT shrink + image-level label sets on the device (deeplab.py:110, weaklabel.cpp:19-31): nearest-neighbour
 // resize of a dense [B][Hg][Wg] ground-truth map (uint8 or int32) to [H][W], stride-2 scan, values >= C void;
 // masks[b] = bit c set <=> class c present; flags[0] |= 1 when a negative label was seen.

@@ -16,8 +16,10 @@
 // never emits 255: every pixel is kept) the count pass is skipped and this is the only launch.
 #include <float.h>
 #include <math.h>
+#include <mutex>
 #include "estep_kernel.cuh"
 #include "bulk_tile.cuh"
+#include "../../include/weaklabel_cuda.h"
 
 namespace wl {
 
@@ -194,6 +196,50 @@ cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long l
                                                              valid, valid_known, bulk_ok);
     if (n_launches) *n_launches += 1;
     return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same two kernels for callers that cannot allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc): the 16 bytes of CeWork live in a file-scope device array instead of a caller's
+// buffer.  Every GPU that loads the library holds the array until exit; every call on a device shares it
+// (it is cleared on the stream at the start of each call), so calls that overlap on one GPU race.
+// In host code `ce_static_scratch` is only a stand-in for the symbol: its device address is resolved
+// once per device, with that device current, by cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t CE_STATIC_BYTES = WEAKLABEL_CE_STATIC_SCRATCH_BYTES;      // the stated maximum (the header documents it)
+constexpr int CE_STATIC_MAX_DEVICES = 64;
+static_assert(sizeof(CeWork) <= CE_STATIC_BYTES, "the static scratch holds one CeWork");
+static __device__ __align__(256) unsigned char ce_static_scratch[CE_STATIC_BYTES];
+
+static cudaError_t ce_static_scratch_address(void **out) {
+    static void *addr[CE_STATIC_MAX_DEVICES];
+    static bool have[CE_STATIC_MAX_DEVICES];
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= CE_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!have[dev]) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, ce_static_scratch);      // the copy of the array on the CURRENT device
+        if (e != cudaSuccess) return e;
+        if (!ptr) return cudaErrorInvalidSymbol;
+        addr[dev] = ptr;
+        have[dev] = true;
+    }
+    *out = addr[dev];
+    return cudaSuccess;
+}
+
+cudaError_t launch_softmax_ce_static(const float *logits, const uint8_t *labels, long long n_pix, int C, int ignore_label,
+                                     float *loss_mean, int *valid, float *dlogits, int sms, cudaStream_t stream,
+                                     int *n_launches) {
+    void *work = nullptr;
+    cudaError_t e = ce_static_scratch_address(&work);
+    if (e != cudaSuccess) return e;
+    return launch_softmax_ce(logits, labels, n_pix, C, ignore_label, loss_mean, valid, dlogits, work, -1, sms, stream,
+                             n_launches);
 }
 
 }  // namespace wl

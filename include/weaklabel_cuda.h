@@ -224,6 +224,21 @@ WL_API int weaklabel_softmax_ce_device(const float *d_logits, const unsigned cha
                                 float *d_loss_mean, int *d_valid, float *d_dlogits,
                                 void *d_work, void *stream);
 
+/* 6b. The same loss without a scratch argument and without any allocation, for callers that
+ *    cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ *    forbid it).  NO COUNTERPART IN THE REFERENCE.
+ *    The 16 bytes of scratch live in a static device array of WEAKLABEL_CE_STATIC_SCRATCH_BYTES
+ *    that every GPU loading the library holds until exit; the call clears it on `stream`.  All
+ *    calls on a device share it: calls that overlap on the GPU (different streams) race -- keep
+ *    them on one stream or order them with events.  The first call on each device resolves the
+ *    array's device address (set-up; make it before a graph capture starts).  n_pix above
+ *    WEAKLABEL_CE_STATIC_MAX_PIXELS is refused (WEAKLABEL_ERR_ARG): the kept-pixel counter in
+ *    the scratch is 32 bits wide.  Arguments and outputs as in weaklabel_softmax_ce_device. */
+#define WEAKLABEL_CE_STATIC_SCRATCH_BYTES 256
+#define WEAKLABEL_CE_STATIC_MAX_PIXELS 2147483647LL
+WL_API int weaklabel_softmax_ce_static(const float *d_logits, const unsigned char *d_labels,
+                                long long n_pix, int C, int ignore_label,
+                                float *d_loss_mean, int *d_valid, float *d_dlogits, void *stream);
 
 /* ---------------------------------------------------------------------------
  * 7. E-step + loss as one call (deeplab.py:120-123 + 182): labels and the softmax
