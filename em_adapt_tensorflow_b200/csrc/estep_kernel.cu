@@ -317,15 +317,14 @@ __global__ void __launch_bounds__(NT, 1) estep_cluster_kernel(const __grid_const
 }
 
 cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream) {
-    static bool attr_done = false;
+    static std::atomic<unsigned long long> attr_done{0};
     const size_t smem = estep_smem_bytes();
     cudaError_t e;
-    if (!attr_done) {
+    if (first_launch_on_device(attr_done)) {
         e = cudaFuncSetAttribute(estep_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(estep_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(n_clusters * p.G));

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 
 namespace wl {
 
@@ -77,6 +78,15 @@ constexpr int OC_F_NO_FASTLABEL = 4;      // every pixel takes the exact (double
 constexpr int OC_F_LOOSE_ZEROS = 8;       // first-generation zero-count bound (counts every pixel above the old max)
 constexpr int OC_F_NO_DIGEST = 16;        // sums: the walker fetches every segment from its owner (no pushed digests)
 constexpr int OC_F_CLASSIC_XCHG = 32;     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
+
+// Function attributes (dynamic shared memory, cluster size) are per DEVICE: a process that drives several GPUs
+// sets them once on each.  `done` is the launcher's static bit mask by device ordinal.
+inline bool first_launch_on_device(std::atomic<unsigned long long> &done) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    const unsigned long long bit = 1ull << dev;
+    return (done.fetch_or(bit) & bit) == 0;
+}
 
 size_t estep_smem_bytes();
 cudaError_t launch_estep(const EStepParams &p, int n_clusters, cudaStream_t stream);

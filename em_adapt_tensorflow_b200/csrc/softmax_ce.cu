@@ -178,11 +178,10 @@ cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long l
     }
     const size_t tile_bytes = (size_t)CE_NT * C * sizeof(float);
     const size_t smem = CE_STAGES * tile_bytes;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<unsigned long long> attr_set{0};
+    if (first_launch_on_device(attr_set)) {
         e = cudaFuncSetAttribute(ce_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(CE_STAGES * CE_NT * MAXC * sizeof(float)));
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     // resident CTAs per SM by shared memory (43 KB per CTA at C = 21 -> 5); one persistent wave
     int per_sm = (int)(220 * 1024 / (smem + 1024));

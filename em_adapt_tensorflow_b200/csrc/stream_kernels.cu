@@ -137,11 +137,10 @@ bool finalize_tiles_applicable(const FinalizeParams &p) {
 cudaError_t launch_finalize_tiles(const FinalizeParams &p, int sms, cudaStream_t stream) {
     const long long n_pix = (long long)p.B * p.N;
     const size_t smem = 2 * (size_t)ST_NT * p.C * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<unsigned long long> attr_set{0};
+    if (first_launch_on_device(attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(finalize_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ST_NT * MAXC * sizeof(float)));
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const long long ntiles = (n_pix + ST_NT - 1) / ST_NT;
     const int bulk_ok = (((uintptr_t)p.map) & 15u) == 0 ? 1 : 0;
@@ -211,11 +210,10 @@ __global__ void __launch_bounds__(ST_NT) fixed_bias_tile_kernel(const float *__r
 cudaError_t launch_fixed_bias(const float *map, long long n_pix, int N, int C, const uint32_t *masks, float bias_bg, float bias_fg,
                               const uint8_t *strong, uint8_t *labels, int sms, cudaStream_t stream) {
     const size_t smem = 2 * (size_t)ST_NT * C * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<unsigned long long> attr_set{0};
+    if (first_launch_on_device(attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(fixed_bias_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ST_NT * MAXC * sizeof(float)));
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const long long ntiles = (n_pix + ST_NT - 1) / ST_NT;
     const int bulk_ok = (((uintptr_t)map) & 15u) == 0 ? 1 : 0;
