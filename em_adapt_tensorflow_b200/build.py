@@ -70,7 +70,9 @@ def build(force=False, verbose=False):
             try:
                 if force or _stale():               # another process may have built it meanwhile
                     tmp = "%s.%d.tmp" % (LIB, os.getpid())
-                    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+                    # development knob: extra nvcc flags (e.g. -DWL_SELPROF, -DWL_TRAIL); never set for a product build
+                    extra = os.environ.get("WEAKLABEL_NVCC_EXTRA", "").split()
+                    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
                           ["-o", tmp] + [os.path.join(CSRC, s) for s in SOURCES]
                     if verbose:
                         print(" ".join(cmd))

@@ -264,7 +264,18 @@ struct alignas(16) Misc {
     uint8_t plist[MAXC];
     uint8_t pplist[NPW][MAXC];          // the producers' copy (image t+1)
     uint8_t ord_s[ORD_S];               // class order of the image in work (a skipped step must not cost a global load)
+#ifdef WL_SELPROF
+    unsigned long long tacc[10], tlast; // -DWL_SELPROF: where a selection's time goes (lead thread, ns)
+#endif
 };
+// -DWL_SELPROF (development builds only, WEAKLABEL_NVCC_EXTRA=-DWL_SELPROF): lap timer of the lead thread inside
+// select / fold (slot 9 = discard) and the producers' time per image; read by tools/phase_report.py
+#ifdef WL_SELPROF
+#define SELP(c, i) do { if ((c).p->prof && (c).rank == 0 && (c).tid == 0) { const unsigned long long t_ = gtimer(); \
+        (c).msp()->tacc[i] += t_ - (c).msp()->tlast; (c).msp()->tlast = t_; } } while (0)
+#else
+#define SELP(c, i) do { } while (0)
+#endif
 
 constexpr int NBX = NB + 32;             // + one private zero-margin counter per warp
 struct SelScratch {
@@ -470,6 +481,10 @@ struct Prod {
     int base, n_t;
     uint32_t nbase;           // chunks of earlier images (stage and parity of chunk q: from nbase + q)
     uint64_t pol;             // L2 evict-first policy of the score stream
+#ifdef WL_SELPROF
+    unsigned long long t_wait;
+    uint32_t n_chunks;
+#endif
 };
 
 __device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
@@ -550,6 +565,9 @@ __device__ __forceinline__ void prod_loop(Prod &w, const ChunkGeom &g, int C, co
     for (int q = q0; q < g.nchunks; q += NPW) {
         const uint32_t n = w.nbase + (uint32_t)q;
         const int d = (int)(n % NST);
+#ifdef WL_SELPROF
+        const unsigned long long tw0 = gtimer();
+#endif
         {   // mbar_wait on full_bar[d] (bounded)
             const uint32_t a = full_bar0 + 8u * (uint32_t)d, parity = (n / NST) & 1u;
             uint32_t ok;
@@ -569,6 +587,10 @@ __device__ __forceinline__ void prod_loop(Prod &w, const ChunkGeom &g, int C, co
         if (q + NPW < g.nchunks) asm volatile("cp.async.wait_group 1;\n" ::: "memory");
         else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
         __syncwarp();
+#ifdef WL_SELPROF
+        w.t_wait += gtimer() - tw0;
+        w.n_chunks++;
+#endif
         int npx, lead, nh, t0, nfl;
         uint32_t bytes;
         chunk_shape(g, C, q, npx, lead, nh, bytes, t0, nfl);
@@ -819,7 +841,21 @@ __device__ __forceinline__ void producer_main(const EStepParams &p, Misc *ms, un
         float *planes = p.planes + (size_t)(slot * 2 + q) * (size_t)(p.C + 2) * p.Npad;
         uint8_t *absidx = p.absent_idx + (size_t)(slot * 2 + q) * p.Npad;
         asm volatile("bar.sync 2, %0;\n" ::"n"(NPW * 32) : "memory");   // every stage of the ring is drained
+#ifdef WL_SELPROF
+        w.t_wait = 0ull; w.n_chunks = 0u;
+        const unsigned long long tp0 = gtimer();
+#endif
         prod_image(w, b, q, planes, absidx);
+#ifdef WL_SELPROF
+        if (p.prof && w.pw == 0 && w.lane == 0) {
+            uint32_t rk;
+            asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(rk));
+            if (rk == 0) {
+                unsigned long long *pr = p.prof + (size_t)b * 32;
+                pr[13] = w.t_wait; pr[14] = gtimer() - tp0; pr[15] = w.n_chunks; pr[12] = tp0;
+            }
+        }
+#endif
         __threadfence();                                        // my plane/E0 stores have reached the L2 (the
         __syncwarp();                                           // E0 tile is fetched from there by the copy engine)
         if (w.lane == 0) mbar_arrive(&ms->ready_bar[q]);        // release: planes and statistics of my chunks
@@ -1276,6 +1312,7 @@ __device__ __forceinline__ Located locate(Cx<NT_> &c, uint32_t r) {
     }
     if (c.tid == NT_ - 1) s->lcount = 0u;
     const uint32_t (*box)[MBW] = exchange(c, NSB);
+    SELP(c, 1);
     // every warp finds the super bin itself (64 sums x G CTAs)
     int S = -1;
     uint32_t preS = 0u;
@@ -1405,9 +1442,12 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
     *zeros = 0xffffffffu;
     for (int guard = 0; guard < 6; guard++) {
         uint32_t *h = ss->hist[c.hround & 1u];          // zeroed since its last use
+        SELP(c, 9);
         if (window) hist_pass_win<NT_, QPT>(c, ta, base, h);
         else hist_pass_range<NT_, QPT>(c, ta, lo, hi, sh, h);
+        SELP(c, 0);
         const Located L = locate(c, r);
+        SELP(c, 2);
         // the histogram of the PREVIOUS round is no longer read by any peer (they all took part in this
         // round's exchange after their fine-bin reads): clear it for the next round
         {
@@ -1443,6 +1483,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
                     }
                 }
             });
+            SELP(c, 3);
             const int fb = L.bin & (SUBB - 1);
             const uint32_t mine = ss->fine[c.rank][fb];
             uint32_t off = 0;
@@ -1458,6 +1499,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
                 }
                 mbar_wait(&c.msp()->xbar[par], (c.xround >> 1) & 1u, c.p, 403);
                 c.xround++;
+                SELP(c, 4);
             } else if (c.G > 1) {
                 csync<NT_>();
                 for (uint32_t i = c.tid; i < (uint32_t)c.G * mine; i += NT_) {
@@ -1473,6 +1515,7 @@ __device__ __forceinline__ float select_margin(Cx<NT_> &c, uint32_t ta, uint32_t
             uint32_t key;
             if (L.cnt <= (uint32_t)RCMAX && !(c.p->flags & OC_F_NO_RANKCOUNT)) key = local_select_rank(c, ss->gather, L.cnt, r);
             else { key = local_select_hist(c, ss->gather, L.cnt, r, klo, khi); csync<NT_>(); }
+            SELP(c, 5);
             return __uint_as_float(key);
         }
         // heavy ties or a coarse (out-of-window) bin: narrow the bracket and bin again
@@ -1964,6 +2007,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         unsigned long long *prof = p.prof ? p.prof + (size_t)c.b * 32 : nullptr;
         unsigned long long t_acq = 0ull, t_sel = 0ull, t_fold = 0ull;
         if (prof && lead_thread) prof[0] = gtimer();
+#ifdef WL_SELPROF
+        if (lead_thread) for (int i = 0; i < 10; i++) ms->tacc[i] = 0ull;
+#endif
         const ImageMeta *im = p.meta + c.b;
         c.mask = im->mask;
         c.P = im->P;
@@ -2125,6 +2171,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                             *Ep = E;
                         });
                         tm_wait_st();
+                        SELP(c, 6);
                         if (sl) c.dirty1 = true; else c.dirty0 = true;
                         if (track_zeros) {
                             for (int o = 16; o; o >>= 1) {
@@ -2145,6 +2192,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                                 if (c.lane == 0) { uint32_t *ob = outbox(c); ob[0] = a0; ob[1] = a1; ob[2] = a2; ob[3] = 0u; }
                             }
                             const uint32_t (*box)[MBW] = exchange(c, 4);
+                            SELP(c, 7);
                             uint32_t gall_s = 0u, gnew_s = 0u, znew_s = 0u;
                             for (int q = 0; q < c.G; q++) { gall_s += box[q][0]; gnew_s += box[q][1]; znew_s += box[q][2]; }
                             // Pixels that leave the zero-margin set of another class: those the folded class newly
@@ -2169,6 +2217,7 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                         else { if (c.dirty0) plane_store<NT_, QPT>(c, plane, 0); c.res0 = -1; c.dirty0 = false; }
                     }
                     csync<NT_>();
+                    SELP(c, 8);
                     if (prof && lead_thread) t_fold += gtimer() - tq2;
                 }
                 if (lead_thread) p.bias_out[((size_t)c.b * p.num_iter + j) * p.C + t] = bias;
@@ -2282,6 +2331,9 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
         if (prof && lead_thread) {
             prof[5] = gtimer();
             prof[6] = nsel;
+#ifdef WL_SELPROF
+            for (int i = 0; i < 9; i++) { prof[23 + i] = ms->tacc[i]; ms->tacc[i] = 0ull; }
+#endif
             prof[7] = (unsigned long long)c.P;
         }
     }

@@ -28,3 +28,16 @@ if t.shape[1] >= 32 and t[:, 8].any():
     if t[:, 14].any():
         print("producer warp 0 of CTA 0, per image (us): streaming %.1f, of which waiting for its stages %.1f; chunks %.0f -> %.2f us per chunk" % (
             t[:, 14].mean() / 1e3, t[:, 13].mean() / 1e3, t[:, 15].mean(), (t[:, 14] / np.maximum(t[:, 15], 1)).mean() / 1e3))
+    if t[:, 23:32].any():          # library built with -DWL_SELPROF: laps of the lead thread inside select / fold
+        lap = ["hist pass", "exchange 1 (super bins)", "locate + fine bins", "gather pass", "gather exchange", "local select",
+               "fold pass", "fold exchange", "fold tail"]
+        for p in sorted(set(P)):
+            m = (P == p) & has
+            if m.any():
+                print("P=%d laps per selection (us): " % p + "  ".join("%s %.2f" % (n, (t[m, 23 + i] / sel[m] / 1e3).mean()) for i, n in enumerate(lap)))
+    if t[:, 14].any():
+        for p in sorted(set(P)):
+            m = P == p
+            print("P=%d producer warp 0 of CTA 0: streaming %.1f us (waiting for stages %.1f), %.0f chunks -> %.2f us per chunk; stream start to image claimed %.1f us" % (
+                p, t[m, 14].mean() / 1e3, t[m, 13].mean() / 1e3, t[m, 15].mean(), (t[m, 14] / np.maximum(t[m, 15], 1)).mean() / 1e3,
+                ((t[m, 0] - t[m, 12]) / 1e3).mean()))
