@@ -390,7 +390,31 @@ def extra_legs(wl, torch, dev, fmap, labels, plan, peak):
                                       gbs=n3 * both / ms_both / 1e6, frac=n3 * both / ms_both / 1e6 / peak,
                                       alg_bytes_per_pixel=both, status=pl3.status(),
                                       note="260 MB of scores, L2 flushed between launches")
+    # -- the same config with the scores = the 41 x 41 fc8 tensor up-sampled (network.py:40).  Fused: the
+    #    producers interpolate the present classes, nothing of 84 B/pixel is ever written or read; against up-sampling
+    #    into HBM first (the materialising kernel + the ordinary E-step).  Its own denominator: no HBM roofline is claimed.
+    fc3 = torch.randn((f3.shape[0], 41, 41, C), device=dev, generator=torch.Generator(device=dev).manual_seed(5)) * 3.0
+    up3 = torch.empty_like(t3)
+    ms_fused = timed(lambda: pl3.labels_upsampled(fc3, out=out3), 10, torch, flush=flush)
+    fused_lab = out3.clone()
+
+    def mat3():
+        wl.upsample_bilinear(fc3, 321, 321, out=up3)
+        pl3.labels(up3, out=out3)
+    ms_mat = timed(mat3, 10, torch, flush=flush)
+    ms_up = timed(lambda: wl.upsample_bilinear(fc3, 321, 321, out=up3), 10, torch, flush=flush)
+    legs["config3_fused_upsample_41_to_321"] = dict(
+        fused_labels_ms=ms_fused, upsample_then_labels_ms=ms_mat, upsample_alone_ms=ms_up,
+        upsample_write_gbs=n3 * 4 * C / ms_up / 1e6, gpixel_s=n3 / ms_fused / 1e6,
+        identical_labels=bool(torch.equal(fused_lab, out3)), status=pl3.status(),
+        note="labels of the E-step on resize_bilinear(fc8 41x41 -> 321x321): interpolated inside the producers vs "
+             "materialised first (84 B/pixel written + read)")
     pl3.close()
+    # -- the same at the metric's shape: 256 x 513 x 513 from 65 x 65 (the resident plan and its label sets)
+    fc5 = torch.randn((B, 65, 65, C), device=dev, generator=torch.Generator(device=dev).manual_seed(6)) * 3.0
+    ms_f5 = timed(lambda: plan.labels_upsampled(fc5, out=labels), 5, torch)
+    legs["fused_upsample_65_to_513x256"] = dict(fused_labels_ms=ms_f5, gpixel_s=npx / ms_f5 / 1e6, status=plan.status(),
+                                                note="no 84 B/pixel stream at all: bound by the producers' interpolation and the selection chain")
     return legs
 
 

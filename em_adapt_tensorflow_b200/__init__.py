@@ -8,5 +8,5 @@ reference's own interface for this path.
 """
 from ._lib import WeakLabelError, lib_path, load            # noqa: F401
 from .estep import estep, estep_c                            # noqa: F401
-from .plan import EStepPlan, OrderStream, draws_for, label_set, label_set_device, softmax_ce, fixed_bias_labels   # noqa: F401
+from .plan import EStepPlan, OrderStream, draws_for, label_set, label_set_device, softmax_ce, fixed_bias_labels, upsample_bilinear   # noqa: F401
 from .shard import shard_range, draws_before, positioned_stream, draw_order   # noqa: F401

@@ -87,6 +87,9 @@ def load():
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.weaklabel_softmax_ce_static.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.weaklabel_upsample_bilinear_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                     C.c_void_p, C.c_void_p]
+    L.weaklabel_estep_labels_upsampled_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     _lib = L
     return L
 
@@ -107,4 +110,5 @@ EXPORTS = ["e_step", "e_step_labels_device", "weaklabel_last_error", "weaklabel_
            "weaklabel_softmax_ce_device", "weaklabel_plan_prepare_async", "weaklabel_label_set_device",
            "weaklabel_plan_prepare_device_gt", "weaklabel_plan_status", "weaklabel_estep_ce_device",
            "weaklabel_estep_labels_dlpack", "weaklabel_plan_set_outputs", "weaklabel_fixed_bias_labels_device",
-           "weaklabel_softmax_ce_static"]
+           "weaklabel_softmax_ce_static", "weaklabel_upsample_bilinear_device",
+           "weaklabel_estep_labels_upsampled_device"]

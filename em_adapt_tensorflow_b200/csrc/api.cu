@@ -554,10 +554,18 @@ extern "C" WL_API int weaklabel_plan_prepare_device_gt(weaklabel_plan *pl, const
     return weaklabel_plan_prepare_async(pl, pl->present_tmp.data(), suppress_others, num_iter, margin_others, bg, fg, rng, stream);
 }
 
+// up_src != NULL: fused bilinear up-sampling -- d_map is ignored, the scores are interpolated from the
+// low-resolution tensor up_src [B][up_h][up_w][C] inside the on-chip kernel (labels only)
 static int run_estep(weaklabel_plan *pl, const float *d_map, long long batch_stride, long long pixel_stride,
-                     unsigned char *d_labels, void *stream, int want_sums) {
-    if (!pl || !d_map) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_labels_device: NULL argument");
+                     unsigned char *d_labels, void *stream, int want_sums, const float *up_src = nullptr,
+                     int up_h = 0, int up_w = 0) {
+    if (!pl || (!d_map && !up_src)) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_labels_device: NULL argument");
     if (!pl->prepared) return fail(WEAKLABEL_ERR_STATE, "plan not prepared");
+    if (up_src) {
+        d_map = up_src;                              // never dereferenced as a map; keeps the checks below uniform
+        batch_stride = (long long)pl->N * pl->C;
+        pixel_stride = pl->C;
+    }
     if (pixel_stride < pl->C || (pl->B > 1 && batch_stride < (long long)(pl->N - 1) * pixel_stride + pl->C))
         return fail(WEAKLABEL_ERR_ARG, "strides overlap: batch %lld pixel %lld", batch_stride, pixel_stride);
     if (((uintptr_t)d_map & 3u) != 0) return fail(WEAKLABEL_ERR_ARG, "d_map is not 4-byte aligned");
@@ -580,6 +588,14 @@ static int run_estep(weaklabel_plan *pl, const float *d_map, long long batch_str
         return fail(WEAKLABEL_ERR_ARG, "on-chip path forced but not applicable (needs suppress_others, margin >= 0, "
                     "contiguous pixels)");
     const int path = pl->tune_path ? pl->tune_path : (oc_ok ? 2 : 1);
+    if (up_src && path != 2)
+        return fail(WEAKLABEL_ERR_STATE, "fused up-sampling runs in the on-chip kernel only (needs suppress_others, margin >= 0 "
+                    "and a shape that kernel covers)");
+    if (up_src) {
+        p.up_src = up_src; p.up_h = up_h; p.up_w = up_w; p.up_W = pl->W;
+        p.up_sy = (float)up_h / (float)pl->H;        // CalculateResizeScale: in_size / static_cast<float>(out_size)
+        p.up_sx = (float)up_w / (float)pl->W;
+    }
     int slots_used = pl->slots;
     p.Npad = pl->Npad; p.sub_px = pl->sub_px;
     if (path == 2) {
@@ -620,6 +636,34 @@ extern "C" WL_API int weaklabel_estep_labels_device(weaklabel_plan *pl, const fl
                                              long long batch_stride, long long pixel_stride,
                                              unsigned char *d_labels, void *stream) {
     return run_estep(pl, d_map, batch_stride, pixel_stride, d_labels, stream, pl ? pl->want_sums : 1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// bilinear up-sampling of the fc8 scores (network.py:40): materialised, and fused into the E-step
+// ---------------------------------------------------------------------------------------------
+extern "C" WL_API int weaklabel_upsample_bilinear_device(const float *d_src, int B, int h, int w, int C, int H, int W,
+                                                  float *d_dst, void *stream) {
+    if (!d_src || !d_dst) return fail(WEAKLABEL_ERR_ARG, "weaklabel_upsample_bilinear_device: NULL argument");
+    if (B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0 || C <= 0 || C > WEAKLABEL_MAX_CLASSES)
+        return fail(WEAKLABEL_ERR_ARG, "bad shape");
+    if ((long long)H * W * C >= (1ll << 31) || (long long)h * w * C >= (1ll << 31))
+        return fail(WEAKLABEL_ERR_ARG, "image too large: H*W*C and h*w*C must stay below 2^31");
+    if (weaklabel_device_count() <= 0)
+        return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
+    CUDA_TRY(launch_upsample_bilinear(d_src, B, h, w, C, H, W, d_dst, (cudaStream_t)stream));
+    return WEAKLABEL_OK;
+}
+
+// Labels of the E-step run on the UP-SAMPLED scores, which are never materialised: the plan is prepared for the
+// full-resolution shape (B, H, W, C); d_fc8 is the contiguous low-resolution tensor [B][h][w][C].  Labels only:
+// there is no full-resolution map to rewrite.  When the on-chip kernel does not cover the configuration the call
+// fails (materialise with weaklabel_upsample_bilinear_device and use weaklabel_estep_labels_device instead).
+extern "C" WL_API int weaklabel_estep_labels_upsampled_device(weaklabel_plan *pl, const float *d_fc8, int h, int w,
+                                                       unsigned char *d_labels, void *stream) {
+    if (!pl || !d_fc8 || !d_labels) return fail(WEAKLABEL_ERR_ARG, "weaklabel_estep_labels_upsampled_device: NULL argument");
+    if (h <= 0 || w <= 0 || (long long)h * w * pl->C >= (1ll << 31)) return fail(WEAKLABEL_ERR_ARG, "bad low-resolution shape %d x %d", h, w);
+    if (((uintptr_t)d_fc8 & 3u) != 0) return fail(WEAKLABEL_ERR_ARG, "d_fc8 is not 4-byte aligned");
+    return run_estep(pl, nullptr, 0, 0, d_labels, stream, 0, d_fc8, h, w);
 }
 
 extern "C" WL_API int weaklabel_plan_set_outputs(weaklabel_plan *pl, int with_sums) {

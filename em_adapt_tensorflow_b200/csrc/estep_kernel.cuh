@@ -69,6 +69,11 @@ struct EStepParams {
                               // 0: labels only -- the two order-exact sums are formed only for images in which a
                               //    pixel's argmax can depend on the rounding of the shift (NaN elsewhere)
     unsigned long long *prof2; // [B][32] fine-grained phase accumulators (ns) or NULL
+    // fused bilinear up-sampling (network.py:40): when up_src != NULL the scores of pixel (y, x) are NOT read from
+    // `map` but interpolated from the low-resolution tensor up_src [B][up_h][up_w][C] (upsample.cuh); on-chip kernel only
+    const float *up_src;
+    int up_h, up_w, up_W;      // low-resolution extent; width of the full-resolution image (N = H * up_W)
+    float up_sy, up_sx;        // up_h / (float)H, up_w / (float)W
 };
 
 // switches of the on-chip kernel: a set bit turns the named optimisation OFF (falls back to the simpler code path)
@@ -131,6 +136,9 @@ cudaError_t launch_softmax_ce(const float *logits, const uint8_t *labels, long l
 cudaError_t launch_softmax_ce_static(const float *logits, const uint8_t *labels, long long n_pix, int C, int ignore_label,
                                      float *loss_mean, int *valid, float *dlogits, int sms, cudaStream_t stream,
                                      int *n_launches);
+
+// tf.image.resize_bilinear (TF1 defaults, network.py:40) of src [B][h][w][C] to dst [B][H][W][C], materialised (stream_kernels.cu)
+cudaError_t launch_upsample_bilinear(const float *src, int B, int h, int w, int C, int H, int W, float *dst, cudaStream_t stream);
 
 // GT shrink + image-level label sets on the device (deeplab.py:110, weaklabel.cpp:19-31): nearest-neighbour
 // resize of a dense [B][Hg][Wg] ground-truth map (uint8 or int32) to [H][W], stride-2 scan, values >= C void;

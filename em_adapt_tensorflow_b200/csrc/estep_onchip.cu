@@ -35,6 +35,7 @@
 #include <math.h>
 #include "estep_kernel.cuh"
 #include "seqsum.cuh"
+#include "upsample.cuh"
 
 namespace wl {
 namespace oc {
@@ -469,7 +470,7 @@ __device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, doub
 // A LIGHT image: one or two present classes, both planes resident in tensor memory for the whole image, no
 // suppressed absent maximum to keep (that needs the whole pixel): see prod_chunk_light / plane_load_light.
 __device__ __forceinline__ bool image_is_light(const EStepParams &p, int P, int cls0) {
-    return p.light_ok && P <= 2 && !(P == 1 && P < p.C && cls0 != 0) && !(p.flags & OC_F_NO_RESIDENT);
+    return p.light_ok && P <= 2 && !(P == 1 && P < p.C && cls0 != 0) && !(p.flags & OC_F_NO_RESIDENT) && !p.up_src;
 }
 
 struct Prod {
@@ -676,6 +677,84 @@ __device__ __forceinline__ void prod_chunk_light(const float *spx, int C, int np
     }
 }
 
+// Fused up-sampling (network.py:40): nothing is streamed.  Each lane forms the scores of the PRESENT classes of its
+// pixel from the four taps of the low-resolution tensor and leaves the same planes, E0, absent maximum and statistics
+// as the streaming paths.  The low-resolution rows a tile needs (its H / G output rows map to ~ h / G + 2 of them) are
+// copied into the idle staging ring first -- the L1 of this kernel is a few KB beside 220 KB of shared memory, taps out
+// of the L2 made the loop latency-bound -- unless they do not fit (then the taps stay global).  Kept OUT of the kernel
+// body: its registers must not disturb the allocation of the streaming paths (the kernel sits at the 64-register cap).
+template <bool STAGED>
+__device__ __forceinline__ void prod_upsampled_loop(const EStepParams &p, const float *src, int row0, int pw, int lane, int base, int n_t,
+                                                    const uint8_t *pl, int P, int first_absent, int need_abs, float *planes,
+                                                    uint8_t *absidx, ProdStats &st) {
+    float *absmax = planes + (size_t)p.C * p.Npad;
+    float *e0pl = planes + (size_t)(p.C + 1) * p.Npad;
+    const float margin = p.margin;
+    const int pl0 = pl[0];
+    const int shift_o = row0 * p.up_w * p.C;           // staged copy: offsets are relative to low-resolution row row0
+    for (int t0 = pw * 32; t0 < n_t; t0 += NPW * 32) {
+        const int t = t0 + lane;
+        if (t >= n_t) continue;
+        const int i = base + t;
+        const int y = i / p.up_W, x = i - y * p.up_W;
+        UpTap tap = up_tap(y, x, p.up_h, p.up_w, p.C, p.up_sy, p.up_sx);
+        if (STAGED) { tap.o00 -= shift_o; tap.o01 -= shift_o; tap.o10 -= shift_o; tap.o11 -= shift_o; }
+        float E = FLT_MIN, mn = FLT_MAX;
+        uint32_t at = 0u, eq = 0u;                 // classes that hold the running max: count, mask of the first four
+        for (int k = 0; k < P; k++) {
+            const float v = up_value<!STAGED>(src, tap, pl[k]);
+            __stcg(planes + (size_t)k * p.Npad + i, v);
+            if (v > E) { E = v; at = 1u; eq = (k < 4) ? (1u << k) : 0u; }
+            else if (v == E) { at++; if (k < 4) eq |= 1u << k; }
+            if (v < mn) mn = v;
+        }
+        __stcg(e0pl + i, E);
+        if (need_abs) {
+            const float xv = mn;                   // P == 1: the one present score
+            const float low = __fsub_rn(xv, margin);
+            float amax = -INFINITY, tf = -INFINITY;
+            for (int k = 0; k < p.C; k++) {
+                if (k == pl0) continue;
+                float a = up_value<!STAGED>(src, tap, k);
+                if (a > xv) a = low;
+                amax = fmaxf(amax, a);
+                if (k == first_absent) tf = a;
+            }
+            __stcg(absmax + i, amax);
+            absidx[i] = (uint8_t)((tf == amax) ? first_absent : 254);
+        }
+        st.zc0 += eq & 1u; st.zc1 += (eq >> 1) & 1u; st.zc2 += (eq >> 2) & 1u; st.zc3 += (eq >> 3) & 1u;
+        st.ties += (at >= 2u) ? 1u : 0u;
+        st.dmx = fmaxf(st.dmx, __fsub_rn(E, mn));
+        st.esum += E;
+    }
+}
+__device__ __noinline__ void prod_upsampled(const EStepParams *pp, int b, int pw, int lane, int base, int n_t, const uint8_t *pl,
+                                            int P, int first_absent, int need_abs, float *planes, uint8_t *absidx,
+                                            float *staging, ProdStats *out) {
+    const EStepParams &p = *pp;
+    const float *src = p.up_src + (long long)b * p.up_h * p.up_w * p.C;
+    ProdStats st = *out;
+    if (n_t > 0) {
+        // low-resolution rows touched by the output rows of my tile: lower tap of the first, upper tap of the last
+        const int ya = base / p.up_W, yb = (base + n_t - 1) / p.up_W;
+        const int r0 = (int)__fmul_rn((float)ya, p.up_sy), r1 = min((int)__fmul_rn((float)yb, p.up_sy) + 1, p.up_h - 1);
+        const int nfl = (r1 - r0 + 1) * p.up_w * p.C;
+        if ((size_t)nfl * sizeof(float) <= (size_t)NST * STAGE_BYTES) {
+            const float *g = src + (size_t)r0 * p.up_w * p.C;
+            for (int f = pw * 32 + lane; f < nfl; f += NPW * 32) staging[f] = __ldg(g + f);
+            asm volatile("bar.sync 2, %0;\n" ::"n"(NPW * 32) : "memory");       // the four producer warps: rows staged
+            prod_upsampled_loop<true>(p, staging, r0, pw, lane, base, n_t, pl, P, first_absent, need_abs, planes, absidx, st);
+        } else {
+            asm volatile("bar.sync 2, %0;\n" ::"n"(NPW * 32) : "memory");       // (same barrier count on both paths)
+            prod_upsampled_loop<false>(p, src, 0, pw, lane, base, n_t, pl, P, first_absent, need_abs, planes, absidx, st);
+        }
+    } else {
+        asm volatile("bar.sync 2, %0;\n" ::"n"(NPW * 32) : "memory");
+    }
+    *out = st;
+}
+
 // one image: chunks q with (nbase + q) % NPW == pw of the CTA's tile
 __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *planes, uint8_t *absidx) {
     const EStepParams &p = *w.p;
@@ -711,6 +790,12 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     g.bar_s = smem_u32(&w.msp()->full_bar[0]);
     g.pol = w.pol;
     g.pf_ahead = p.pf_ahead;
+    if (p.up_src) {
+        ProdStats ust = {0u, 0u, 0u, 0u, 0u, 0.f, 0.f};
+        prod_upsampled(&p, b, w.pw, w.lane, w.base, w.n_t, pl, P, first_absent, need_abs ? 1 : 0, planes, absidx,
+                       reinterpret_cast<float *>(w.stagingp()), &ust);
+        zc0 = ust.zc0; zc1 = ust.zc1; zc2 = ust.zc2; zc3 = ust.zc3; ties = ust.ties; dmx = ust.dmx; esum = ust.esum;
+    } else {
     // every stage is free (the producers met after the previous image): fill the ring
     for (int q = q0; q < nchunks && q < NST; q += NPW) prod_issue2(g, p.C, w.lane, q, (int)((w.nbase + (uint32_t)q) % NST), w, img);
     const int C = p.C;
@@ -804,6 +889,7 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
         });
     }
     w.nbase += (uint32_t)nchunks;
+    }   // (streamed image)
     // my share of the tile's statistics
     uint32_t dm = __float_as_uint(dmx);               // margins are >= +0: the bit patterns order like the values
     for (int o = 16; o; o >>= 1) {
@@ -1661,9 +1747,19 @@ __device__ __forceinline__ int plane_acquire(Cx<NT_> &c, int plane) {
 // Exact label of one pixel from the final scores of the present classes (vals[pl], float) and the
 // original scores of the absent ones, exactly as the reference forms them: suppressed (weaklabel.cpp:
 // 45-65), shifted in double, rounded to float (:110), first maximum (deeplab.py:123).
+// The C original scores of pixel i of image b: a row of the map -- or, with fused up-sampling, the values the
+// producers formed for it, interpolated again into loc (same taps, same operations: same bits).
+__device__ __noinline__ void up_row(const EStepParams &p, int b, int i, float *loc) {
+    const int y = i / p.up_W, x = i - y * p.up_W;
+    const UpTap tap = up_tap(y, x, p.up_h, p.up_w, p.C, p.up_sy, p.up_sx);
+    const float *src = p.up_src + (long long)b * p.up_h * p.up_w * p.C;
+    for (int k = 0; k < p.C; k++) loc[k] = up_value<true>(src, tap, k);
+}
 template <typename V>
 static __device__ __forceinline__ int label_exact(const EStepParams &p, uint32_t mask, int b, int i, double shift, V &&val) {
+    float loc[MAXC];
     const float *px = p.map + (long long)b * p.s0 + (long long)i * p.s2;
+    if (p.up_src) { up_row(p, b, i, loc); px = loc; }
     float m = FLT_MAX;
     for (int k = 0; k < p.C; k++)
         if ((mask >> k) & 1u) { const float t = px[k]; if (t < m) m = t; }
@@ -1768,8 +1864,10 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
                 if (d == 0.f && !exact_all && 4 * q + e < c.n_t) {
                     // an exact tie of the two present classes goes to the lower index whatever the shift -- unless
                     // an absent class comes within the guard of them
-                    bad = has_absent && !(__fsub_rn(lo, absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
-                                                                   c.mask, p.C, p.margin)) > guard);
+                    // (fused up-sampling: there is no map row to look at -- the pixel is left to pass B, which interpolates it)
+                    bad = has_absent && (p.up_src != nullptr ||
+                                         !(__fsub_rn(lo, absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
+                                                                    c.mask, p.C, p.margin)) > guard));
                 }
                 lab4 |= (uint32_t)(hi > lo ? hi_cls : lo_cls) << (8 * e);
                 un4 |= (bad ? 1u : 0u) << e;
@@ -1804,7 +1902,8 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
                 bool bad = exact_all || !(__fsub_rn(best[e], near_[e]) > guard);
                 if (bad && !exact_all && near_[e] < best[e]) bad = !pair_stays_distinct(near_[e], best[e], ashift, spos);
                 if (has_absent && !have_abs && near_[e] == -INFINITY && !bad && 4 * q + e < c.n_t)
-                    bad = !(__fsub_rn(best[e], absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
+                    bad = p.up_src != nullptr ||
+                          !(__fsub_rn(best[e], absent_max(p.map + (long long)c.b * p.s0 + (long long)(c.base + 4 * q + e) * p.s2,
                                                           c.mask, p.C, p.margin)) > guard);
                 if (have_abs && !(__fsub_rn(best[e], ava[e]) > guard)) bad = true;
                 lab4 |= (uint32_t)bi[e] << (8 * e);

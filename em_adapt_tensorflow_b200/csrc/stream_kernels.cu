@@ -12,6 +12,7 @@
 #include <math.h>
 #include "estep_kernel.cuh"
 #include "bulk_tile.cuh"
+#include "upsample.cuh"
 
 namespace wl {
 
@@ -219,6 +220,81 @@ cudaError_t launch_fixed_bias(const float *map, long long n_pix, int N, int C, c
     const int bulk_ok = (((uintptr_t)map) & 15u) == 0 ? 1 : 0;
     fixed_bias_tile_kernel<<<stream_grid(smem, ntiles, sms), ST_NT, smem, stream>>>(map, n_pix, N, C, masks, bias_bg, bias_fg, strong,
                                                                                    labels, bulk_ok);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// tf.image.resize_bilinear (network.py:40), materialised: dst [B][H][W][C] from src [B][h][w][C].
+// A CTA owns a run of consecutive output rows.  The two low-resolution rows an output row interpolates between are
+// staged in shared memory (and kept while the following output rows map to the same pair: H / h of them do); one
+// thread per output FLOAT of the row, so the 4 * C-byte pixel rows leave fully coalesced.  Write-bound:
+// 4 * C bytes per output pixel.  STAGED = false (a low-resolution row pair beyond shared memory): taps from global.
+// ---------------------------------------------------------------------------------------------
+constexpr int UP_NT = 256;
+template <bool STAGED>
+__global__ void __launch_bounds__(UP_NT) upsample_bilinear_kernel(const float *__restrict__ src, int h, int w, int C, int H, int W,
+                                                                  float sy, float sx, float *__restrict__ dst, int rows, int rows_per_cta,
+                                                                  unsigned int inv_c) {
+    extern __shared__ __align__(16) float up_rows[];         // [2][w * C]
+    const int wc = w * C, WC = W * C;
+    const int r_begin = blockIdx.x * rows_per_cta, r_end = min(rows, r_begin + rows_per_cta);
+    int have_b = -1, have_y0 = -1;
+    for (int r = r_begin; r < r_end; r++) {
+        const int b = r / H, y = r - b * H;
+        const float fy = __fmul_rn((float)y, sy);
+        const int y0 = (int)fy, y1 = min(y0 + 1, h - 1);
+        const float ly = __fsub_rn(fy, (float)y0);
+        const float *s0 = src + ((long long)b * h + y0) * wc, *s1 = src + ((long long)b * h + y1) * wc;
+        if (STAGED && (b != have_b || y0 != have_y0)) {       // block-uniform
+            __syncthreads();                                   // the readers of the previous pair are done
+            for (int f = threadIdx.x; f < wc; f += UP_NT) { up_rows[f] = __ldg(s0 + f); up_rows[wc + f] = __ldg(s1 + f); }
+            __syncthreads();
+            have_b = b; have_y0 = y0;
+        }
+        float *drow = dst + (long long)r * WC;
+        for (int f = threadIdx.x; f < WC; f += UP_NT) {
+            const int x = (int)__umulhi((unsigned int)f, inv_c);      // f / C (exact for f * (C - 1) < 2^32)
+            const int cls = f - x * C;
+            const float fx = __fmul_rn((float)x, sx);
+            const int x0 = (int)fx, x1 = min(x0 + 1, w - 1);
+            UpTap t;
+            t.lx = __fsub_rn(fx, (float)x0);
+            t.ly = ly;
+            if (STAGED) {
+                t.o00 = x0 * C; t.o01 = x1 * C; t.o10 = wc + x0 * C; t.o11 = wc + x1 * C;
+                drow[f] = up_value<false>(up_rows, t, cls);
+            } else {
+                t.o00 = x0 * C; t.o01 = x1 * C;
+                t.o10 = (int)(s1 - s0) + x0 * C; t.o11 = (int)(s1 - s0) + x1 * C;
+                drow[f] = up_value<true>(s0, t, cls);
+            }
+        }
+    }
+}
+
+cudaError_t launch_upsample_bilinear(const float *src, int B, int h, int w, int C, int H, int W, float *dst, cudaStream_t stream) {
+    const long long rows_ll = (long long)B * H;
+    if (rows_ll == 0 || W == 0) return cudaSuccess;
+    if (rows_ll >= (1ll << 31)) return cudaErrorInvalidValue;
+    const int rows = (int)rows_ll;
+    // enough CTAs to fill the GPU, few enough that a CTA keeps its staged row pair for several output rows
+    int ctas = 148 * 8;
+    if (ctas > rows) ctas = rows;
+    const int rpc = (rows + ctas - 1) / ctas;
+    ctas = (rows + rpc - 1) / rpc;
+    const unsigned int inv_c = (unsigned int)(((1ull << 32) + (unsigned long long)C - 1ull) / (unsigned long long)C);
+    const size_t smem = (size_t)2 * w * C * sizeof(float);
+    const float sy = (float)h / (float)H, sx = (float)w / (float)W;
+    if (smem <= 200 * 1024) {
+        static std::atomic<unsigned long long> attr_set{0};
+        if (first_launch_on_device(attr_set)) {
+            cudaError_t e = cudaFuncSetAttribute(upsample_bilinear_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return e;
+        }
+        upsample_bilinear_kernel<true><<<ctas, UP_NT, smem, stream>>>(src, h, w, C, H, W, sy, sx, dst, rows, rpc, inv_c);
+    } else {
+        upsample_bilinear_kernel<false><<<ctas, UP_NT, 0, stream>>>(src, h, w, C, H, W, sy, sx, dst, rows, rpc, inv_c);
+    }
     return cudaGetLastError();
 }
 

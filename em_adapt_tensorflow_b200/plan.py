@@ -143,6 +143,20 @@ class EStepPlan:
                                                          fmap.stride(2), out.data_ptr(), self._stream()))
         return out
 
+    def labels_upsampled(self, fc8, out=None):
+        """E-step labels on tf.image.resize_bilinear(fc8, (H, W)) (network.py:40) WITHOUT materialising the
+        up-sampled scores: fc8 is the contiguous low-resolution CUDA float32 tensor [B,h,w,C]; the plan was created
+        and prepared for the full-resolution shape.  -> uint8 [B,H,W], bit-identical to
+        labels(upsample_bilinear(fc8, H, W))."""
+        import torch
+        assert fc8.is_cuda and fc8.dtype == torch.float32 and fc8.dim() == 4 and fc8.is_contiguous()
+        assert fc8.shape[0] == self.B and fc8.shape[3] == self.C
+        if out is None:
+            out = torch.empty((self.B, self.H, self.W), dtype=torch.uint8, device=fc8.device)
+        _lib.check(self._L.weaklabel_estep_labels_upsampled_device(self.handle, fc8.data_ptr(), int(fc8.shape[1]),
+                                                                   int(fc8.shape[2]), out.data_ptr(), self._stream()))
+        return out
+
     def labels_dlpack(self, scores, labels):
         """The DLPack front door (weaklabel_estep_labels_dlpack): `scores` / `labels` are ANY objects with
         __dlpack__ (torch, cupy, jax arrays ...) holding float32 [B,H,W,C] / uint8 [B,H,W] CUDA memory.
@@ -235,6 +249,20 @@ def fixed_bias_labels(fmap, masks, bias_bg, bias_fg, strong=None):
     _lib.check(L.weaklabel_fixed_bias_labels_device(fmap.data_ptr(), B, H, W, Cc, masks.data_ptr(), float(bias_bg), float(bias_fg),
                                                     strong.data_ptr() if strong is not None else None, out.data_ptr(),
                                                     C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
+def upsample_bilinear(fc8, H, W, out=None):
+    """tf.image.resize_bilinear(fc8, (H, W)) with the TF1 defaults (network.py:40), materialised on the device:
+    fc8 CUDA float32 [B,h,w,C] contiguous -> [B,H,W,C]."""
+    import torch
+    assert fc8.is_cuda and fc8.dtype == torch.float32 and fc8.dim() == 4 and fc8.is_contiguous()
+    B, h, w, Cc = (int(v) for v in fc8.shape)
+    if out is None:
+        out = torch.empty((B, int(H), int(W), Cc), dtype=torch.float32, device=fc8.device)
+    with torch.cuda.device(fc8.device):
+        _lib.check(_lib.load().weaklabel_upsample_bilinear_device(fc8.data_ptr(), B, h, w, Cc, int(H), int(W), out.data_ptr(),
+                                                                  torch.cuda.current_stream().cuda_stream))
     return out
 
 

@@ -265,6 +265,23 @@ WL_API int weaklabel_fixed_bias_labels_device(const float *d_map, int B, int H, 
                                        const unsigned char *d_strong, unsigned char *d_labels, void *stream);
 
 /* ---------------------------------------------------------------------------
+ * 7c. Bilinear up-sampling of the fc8 scores (network.py:40: tf.image.resize_bilinear with
+ *    the TF1 defaults align_corners = False, no half-pixel centres; TensorFlow is a
+ *    third-party dependency of the reference, its published kernel is restated in
+ *    csrc/upsample.cuh and oracle/oracle.py).  d_src [B][h][w][C] -> d_dst [B][H][W][C],
+ *    both contiguous float32.
+ *    weaklabel_estep_labels_upsampled_device runs the E-step (deeplab.py:120-123) on the
+ *    up-sampled scores WITHOUT materialising them: the plan is created
+ *    and prepared for the full-resolution shape, d_fc8 is the low-resolution tensor; the
+ *    labels are bit-identical to up-sampling first and calling weaklabel_estep_labels_device.
+ *    On-chip kernel only (suppress_others, margin >= 0); WEAKLABEL_ERR_STATE otherwise.
+ * ------------------------------------------------------------------------- */
+WL_API int weaklabel_upsample_bilinear_device(const float *d_src, int B, int h, int w, int C, int H, int W,
+                                       float *d_dst, void *stream);
+WL_API int weaklabel_estep_labels_upsampled_device(weaklabel_plan *plan, const float *d_fc8, int h, int w,
+                                            unsigned char *d_labels, void *stream);
+
+/* ---------------------------------------------------------------------------
  * 8. DLPack front door.  weaklabel_dltensor is the DLTensor of dlpack.h (dmlc/dlpack,
  *    third-party; restated field by field so that no foreign header is needed).  A
  *    DLManagedTensor begins with its DLTensor, so a pointer taken from a "dltensor"

@@ -47,6 +47,29 @@ def resize_nearest(gt, H, W):
     return gt[:, ys][:, :, xs]
 
 
+def resize_bilinear(x, H, W):
+    """network.py:40 -- tf.image.resize_bilinear(output, (h, w)) with the TF1 defaults (align_corners=False, no
+    half-pixel centres), restated from TensorFlow's published CPU kernel (tensorflow/core/kernels/
+    resize_bilinear_op.cc; third-party to the reference, version unpinned: parity unpinned): per output index
+    in = index * float32(in_size / out_size), lower = int(in), upper = min(lower + 1, in_size - 1), lerp = in - lower;
+    value = top + (bottom - top) * y_lerp with top = tl + (tr - tl) * x_lerp, every step in float32.
+    x: [B,h,w,C] float32 -> [B,H,W,C] float32."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    h, w = x.shape[1], x.shape[2]
+    sy, sx = np.float32(h) / np.float32(H), np.float32(w) / np.float32(W)
+    fy = (np.arange(H, dtype=np.float32) * sy).astype(np.float32)
+    fx = (np.arange(W, dtype=np.float32) * sx).astype(np.float32)
+    y0, x0 = fy.astype(np.int64), fx.astype(np.int64)
+    y1, x1 = np.minimum(y0 + 1, h - 1), np.minimum(x0 + 1, w - 1)
+    ly = (fy - y0.astype(np.float32)).astype(np.float32)[None, :, None, None]
+    lx = (fx - x0.astype(np.float32)).astype(np.float32)[None, None, :, None]
+    tl, tr = x[:, y0][:, :, x0], x[:, y0][:, :, x1]
+    bl, br = x[:, y1][:, :, x0], x[:, y1][:, :, x1]
+    top = (tl + ((tr - tl).astype(np.float32) * lx).astype(np.float32)).astype(np.float32)
+    bot = (bl + ((br - bl).astype(np.float32) * lx).astype(np.float32)).astype(np.float32)
+    return (top + ((bot - top).astype(np.float32) * ly).astype(np.float32)).astype(np.float32)
+
+
 class Oracle:
     """C restatement; batched = B consecutive single-image calls on one RNG stream."""
 

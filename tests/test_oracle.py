@@ -104,3 +104,32 @@ def test_oracle_softmax_ce_against_numpy(oracle):
     sm[np.arange(50), np.minimum(y, 20)] -= 1
     sm[~keep] = 0
     assert np.allclose(grad, sm / keep.sum(), atol=1e-15)
+
+
+def test_oracle_resize_bilinear_against_a_scalar_restatement():
+    """network.py:40: the vectorised restatement of TensorFlow's resize_bilinear kernel against the published
+    per-pixel formulas written out as scalar float32 loops; plus the properties that need no reference:
+    same size = identity, a constant stays constant, the first row/column are copied (lerp 0)."""
+    from oracle.oracle import resize_bilinear
+    rng = np.random.default_rng(3)
+    x = (rng.standard_normal((2, 5, 7, 3)) * 3.0).astype(np.float32)
+    H, W = 13, 11
+    got = resize_bilinear(x, H, W)
+    f32 = np.float32
+    sy, sx = f32(5) / f32(H), f32(7) / f32(W)
+    for b in range(2):
+        for y in range(H):
+            fy = f32(y) * sy
+            y0 = int(fy); y1 = min(y0 + 1, 4); ly = f32(fy - f32(y0))
+            for xo in range(W):
+                fx = f32(xo) * sx
+                x0 = int(fx); x1 = min(x0 + 1, 6); lx = f32(fx - f32(x0))
+                for c in range(3):
+                    tl, tr, bl, br = x[b, y0, x0, c], x[b, y0, x1, c], x[b, y1, x0, c], x[b, y1, x1, c]
+                    top = f32(tl + f32(f32(tr - tl) * lx))
+                    bot = f32(bl + f32(f32(br - bl) * lx))
+                    want = f32(top + f32(f32(bot - top) * ly))
+                    assert got[b, y, xo, c].view(np.uint32) == want.view(np.uint32)
+    assert np.array_equal(resize_bilinear(x, 5, 7), x)
+    assert np.array_equal(resize_bilinear(np.full((1, 3, 3, 2), 1.25, np.float32), 9, 8), np.full((1, 9, 8, 2), 1.25, np.float32))
+    assert np.array_equal(got[:, 0, 0], x[:, 0, 0])
