@@ -41,6 +41,24 @@ static int fail(int code, const char *fmt, ...) {
                         cudaGetErrorString(e__), __FILE__, __LINE__);                         \
     } while (0)
 
+// The library works on the PLAN'S device and leaves the caller's current device as it found it (a process may
+// drive several GPUs; a library call must not move it to another one behind its back).
+struct DeviceScope {
+    int prev = -1;
+    bool moved = false;
+    cudaError_t enter(int dev) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev != dev) {
+            e = cudaSetDevice(dev);
+            moved = (e == cudaSuccess);
+        }
+        return e;
+    }
+    ~DeviceScope() { if (moved) cudaSetDevice(prev); }
+};
+#define ON_DEVICE(dev) DeviceScope device_scope_; CUDA_TRY(device_scope_.enter(dev))
+
 extern "C" WL_API const char *weaklabel_last_error(void) { return g_err.c_str(); }
 extern "C" WL_API int weaklabel_version(void) { return 200; }
 extern "C" WL_API int weaklabel_device_count(void) {
@@ -314,7 +332,7 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
         return fail(WEAKLABEL_ERR_ARG, "image of %lld pixels is too large", (long long)H * W);
     if (weaklabel_device_count() <= 0)
         return fail(WEAKLABEL_ERR_CUDA, "no CUDA device: libweaklabel_cuda has no CPU fallback");
-    CUDA_TRY(cudaSetDevice(device));
+    ON_DEVICE(device);
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 9)
@@ -358,7 +376,8 @@ extern "C" WL_API int weaklabel_plan_create(weaklabel_plan **out, int B, int H, 
 
 extern "C" WL_API void weaklabel_plan_destroy(weaklabel_plan *pl) {
     if (!pl) return;
-    cudaSetDevice(pl->device);
+    DeviceScope scope;
+    scope.enter(pl->device);
     plan_free_geometry(pl);
     if (pl->has_run) cudaStreamSynchronize(pl->last_stream);
     if (pl->has_tables) cudaStreamSynchronize(pl->tables_stream);
@@ -378,7 +397,7 @@ extern "C" WL_API int weaklabel_plan_tune(weaklabel_plan *pl, int cluster_size, 
     if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
     if (cluster_size < 0 || tile_pixels < 0 || max_clusters < 0 || tile_pixels > TS_MAX)
         return fail(WEAKLABEL_ERR_ARG, "bad tuning values");
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     plan_free_geometry(pl);
     pl->tune_G = cluster_size; pl->tune_TS = tile_pixels; pl->tune_slots = max_clusters;
@@ -396,7 +415,7 @@ extern "C" WL_API int weaklabel_plan_last_path(const weaklabel_plan *pl) { retur
 
 extern "C" WL_API int weaklabel_plan_profile(weaklabel_plan *pl, int enable, unsigned long long *out) {
     if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     if (out) CUDA_TRY(cudaMemcpy(out, pl->d_prof, (size_t)pl->B * 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     pl->prof_on = enable != 0;
@@ -451,7 +470,7 @@ extern "C" WL_API int weaklabel_plan_prepare_async(weaklabel_plan *pl, const uns
                 pl->h_order[o] = (uint8_t)pos_of[ord_cls[o]];
             }
     }
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     // one block [sched | meta | order], staged in pinned memory and uploaded with one asynchronous copy
     const size_t osz = pl->h_order.size() > 0 ? pl->h_order.size() : 1;
     const size_t off_meta = ((size_t)B * sizeof(int) + 15) & ~(size_t)15;
@@ -537,7 +556,7 @@ extern "C" WL_API int weaklabel_plan_prepare_device_gt(weaklabel_plan *pl, const
                                                 float bg, float fg, weaklabel_rng *rng, void *stream) {
     if (!pl || !d_gt) return fail(WEAKLABEL_ERR_ARG, "weaklabel_plan_prepare_device_gt: NULL argument");
     if (Hg <= 0 || Wg <= 0) return fail(WEAKLABEL_ERR_ARG, "bad ground-truth size %dx%d", Hg, Wg);
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int B = pl->B, C = pl->C;
     CUDA_TRY(launch_label_set(d_gt, gt_is_int32, B, Hg, Wg, pl->H, pl->W, C, pl->d_masks, pl->d_flags, st));
@@ -569,7 +588,7 @@ static int run_estep(weaklabel_plan *pl, const float *d_map, long long batch_str
     if (pixel_stride < pl->C || (pl->B > 1 && batch_stride < (long long)(pl->N - 1) * pixel_stride + pl->C))
         return fail(WEAKLABEL_ERR_ARG, "strides overlap: batch %lld pixel %lld", batch_stride, pixel_stride);
     if (((uintptr_t)d_map & 3u) != 0) return fail(WEAKLABEL_ERR_ARG, "d_map is not 4-byte aligned");
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     int rc = plan_geometry(pl);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -680,7 +699,7 @@ extern "C" WL_API int weaklabel_estep_finalize_map_device(weaklabel_plan *pl, fl
     if (!pl->last_sums)
         return fail(WEAKLABEL_ERR_STATE, "the last run() was labels-only (weaklabel_plan_set_outputs(plan, 0)): the in-place "
                     "map needs the re-centring sums of every image");
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     FinalizeParams f;
     memset(&f, 0, sizeof f);
     f.map = d_map; f.s0 = batch_stride; f.s2 = pixel_stride;
@@ -716,14 +735,14 @@ extern "C" WL_API int weaklabel_plan_status(weaklabel_plan *pl, int *code) {
     if (!pl) return fail(WEAKLABEL_ERR_ARG, "plan is NULL");
     if (code) *code = 0;
     if (!pl->has_run) return WEAKLABEL_OK;
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     return plan_check_status(pl, code);
 }
 
 extern "C" WL_API int weaklabel_plan_probes(weaklabel_plan *pl, int *order, float *bias, float *mean0, double *mean1) {
     if (!pl || !pl->prepared) return fail(WEAKLABEL_ERR_STATE, "plan not prepared");
-    CUDA_TRY(cudaSetDevice(pl->device));
+    ON_DEVICE(pl->device);
     if (pl->has_run) CUDA_TRY(cudaStreamSynchronize(pl->last_stream));
     int rc = plan_check_status(pl, nullptr);
     if (rc) return rc;

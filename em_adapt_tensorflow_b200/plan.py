@@ -122,12 +122,13 @@ class EStepPlan:
         _lib.check(self._L.weaklabel_plan_status(self.handle, C.byref(code)))
         return code.value
 
-    @staticmethod
-    def _stream():
+    def _stream(self):
+        """The current torch stream of THE PLAN'S device (a process may drive several GPUs: the current device
+        can be another one), else the legacy default stream."""
         try:
             import torch
             if torch.cuda.is_available():
-                return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+                return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         except ImportError:
             pass
         return C.c_void_p(0)
@@ -228,9 +229,10 @@ def label_set_device(gt, H, W, num_classes):
     assert gt.is_cuda and gt.is_contiguous() and gt.dim() == 3 and gt.dtype in (torch.uint8, torch.int32)
     masks = torch.empty(gt.shape[0], dtype=torch.int32, device=gt.device)
     flags = torch.empty(1, dtype=torch.int32, device=gt.device)
-    _lib.check(L.weaklabel_label_set_device(gt.data_ptr(), int(gt.dtype == torch.int32), int(gt.shape[0]), int(gt.shape[1]),
-                                            int(gt.shape[2]), int(H), int(W), int(num_classes), masks.data_ptr(),
-                                            flags.data_ptr(), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    with torch.cuda.device(gt.device):
+        _lib.check(L.weaklabel_label_set_device(gt.data_ptr(), int(gt.dtype == torch.int32), int(gt.shape[0]), int(gt.shape[1]),
+                                                int(gt.shape[2]), int(H), int(W), int(num_classes), masks.data_ptr(),
+                                                flags.data_ptr(), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return masks
 
 
@@ -246,9 +248,10 @@ def fixed_bias_labels(fmap, masks, bias_bg, bias_fg, strong=None):
     out = torch.empty((B, H, W), dtype=torch.uint8, device=fmap.device)
     if strong is not None:
         assert strong.is_cuda and strong.dtype == torch.uint8 and strong.is_contiguous() and strong.numel() == B * H * W
-    _lib.check(L.weaklabel_fixed_bias_labels_device(fmap.data_ptr(), B, H, W, Cc, masks.data_ptr(), float(bias_bg), float(bias_fg),
-                                                    strong.data_ptr() if strong is not None else None, out.data_ptr(),
-                                                    C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    with torch.cuda.device(fmap.device):
+        _lib.check(L.weaklabel_fixed_bias_labels_device(fmap.data_ptr(), B, H, W, Cc, masks.data_ptr(), float(bias_bg), float(bias_fg),
+                                                        strong.data_ptr() if strong is not None else None, out.data_ptr(),
+                                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return out
 
 
@@ -281,8 +284,9 @@ def softmax_ce(logits, labels, ignore_label=255, want_grad=True):
     valid = torch.empty((), dtype=torch.int32, device=logits.device)
     grad = torch.empty_like(logits) if want_grad else None
     work = torch.empty(2, dtype=torch.float64, device=logits.device)
-    _lib.check(L.weaklabel_softmax_ce_device(logits.data_ptr(), labels.data_ptr(), n, Cc, int(ignore_label),
-                                             loss.data_ptr(), valid.data_ptr(),
-                                             grad.data_ptr() if want_grad else None, work.data_ptr(),
-                                             C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    with torch.cuda.device(logits.device):          # the launch goes to the tensors' device, whatever the current one is
+        _lib.check(L.weaklabel_softmax_ce_device(logits.data_ptr(), labels.data_ptr(), n, Cc, int(ignore_label),
+                                                 loss.data_ptr(), valid.data_ptr(),
+                                                 grad.data_ptr() if want_grad else None, work.data_ptr(),
+                                                 C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return loss, valid, grad
