@@ -82,7 +82,8 @@ constexpr int OC_F_NO_RESIDENT = 2;       // evict the class plane after every s
 constexpr int OC_F_NO_FASTLABEL = 4;      // every pixel takes the exact (double) label path
 constexpr int OC_F_LOOSE_ZEROS = 8;       // first-generation zero-count bound (counts every pixel above the old max)
 constexpr int OC_F_NO_DIGEST = 16;        // sums: the walker fetches every segment from its owner (no pushed digests)
-constexpr int OC_F_CLASSIC_XCHG = 32;     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
+constexpr int OC_F_CLASSIC_XCHG = 32;
+constexpr int OC_F_RAGGED_COPIES = 64;    // every chunk as aligned interior + cp.async head / tail floats (no whole-span copies)     // exchanges with plain DSMEM stores + arrive/wait instead of st.async
 
 // Function attributes (dynamic shared memory, cluster size) are per DEVICE: a process that drives several GPUs
 // sets them once on each.  `done` is the launcher's static bit mask by device ordinal.

@@ -515,6 +515,8 @@ struct ChunkGeom {
     uint32_t stage_s, bar_s;  // shared-window addresses of stage 0 / full_bar[0]
     uint64_t pol;
     int pf_ahead;
+    int whole_lo, whole_hi;   // chunks whole_lo .. whole_hi travel as ONE bulk copy of the 16-byte-aligned span around them
+    uint32_t wbytes;          // its size for a full chunk
 };
 __device__ __forceinline__ void chunk_shape(const ChunkGeom &g, int C, int q, int &npx, int &lead, int &nh, uint32_t &bytes, int &t0, int &nfl) {
     if (g.uniform && (q + 1) * g.cpx <= g.n_t) {
@@ -535,6 +537,18 @@ __device__ __forceinline__ void prod_issue2(const ChunkGeom &g, int C, int lane,
     chunk_shape(g, C, q, npx, lead, nh, bytes, t0, nfl);
     const float *g0 = g.gtile + (long long)q * g.cs;
     const uint32_t stage_s = g.stage_s + (uint32_t)d * STAGE_BYTES + 4u * (uint32_t)lead, bar_s = g.bar_s + 8u * (uint32_t)d;
+    if (q >= g.whole_lo && q <= g.whole_hi) {
+        // The chunk sits inside the tensor with at least 12 bytes of it on either side: the copy engine moves the
+        // 16-byte-aligned span AROUND it (up to 3 floats of the neighbouring chunks come along and are ignored), the
+        // first pixel lands at the same stage offset as below.  No per-chunk cp.async, no group to commit.
+        if (lane == 0) {
+            const uint32_t wb = (g.uniform && nfl == g.cs) ? g.wbytes : (uint32_t)(((lead + nfl) * 4 + 15) & ~15);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar_s), "r"(wb) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n"
+                         ::"r"(stage_s - 4u * (uint32_t)lead), "l"(g0 - lead), "r"(wb), "r"(bar_s), "l"(g.pol) : "memory");
+        }
+        return;
+    }
     // the ragged head / tail floats travel as 4-byte asynchronous copies (one cp.async group per chunk and lane:
     // a plain load here would put a global-memory round trip on the issue path of EVERY chunk); lanes 0-2 the
     // head, lanes 3-5 the tail.  The stage is drained by this same warp, which waits for the group.
@@ -790,6 +804,11 @@ __device__ __forceinline__ void prod_image(Prod &w, int b, int par, float *plane
     g.bar_s = smem_u32(&w.msp()->full_bar[0]);
     g.pol = w.pol;
     g.pf_ahead = p.pf_ahead;
+    // whole-span copies read up to 12 bytes before / 15 bytes after a chunk: everywhere but at the two ends of the tensor
+    g.wbytes = (uint32_t)(((g.lead + g.cs) * 4 + 15) & ~15);
+    g.whole_lo = (b == 0 && w.base == 0 && g.lead != 0) ? 1 : 0;
+    g.whole_hi = (b == p.B - 1 && w.base + w.n_t == p.N) ? nchunks - 2 : nchunks - 1;
+    if (p.flags & OC_F_RAGGED_COPIES) { g.whole_lo = 1; g.whole_hi = 0; }
     if (p.up_src) {
         ProdStats ust = {0u, 0u, 0u, 0u, 0u, 0.f, 0.f};
         prod_upsampled(&p, b, w.pw, w.lane, w.base, w.n_t, pl, P, first_absent, need_abs ? 1 : 0, planes, absidx,

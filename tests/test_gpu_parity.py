@@ -273,7 +273,7 @@ def test_errors_are_reported_not_swallowed():
 
 
 OC_FLAGS = {"rankcount_off": 1, "resident_off": 2, "fastlabel_off": 4, "loose_zeros": 8, "digest_off": 16,
-            "classic_xchg": 32, "all_off": 63}
+            "classic_xchg": 32, "ragged_copies": 64, "all_off": 127}
 
 
 @pytest.mark.parametrize("flag", sorted(OC_FLAGS))

@@ -11,7 +11,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 JOBS = [
-    ("c1_41_p2", "1,0,0", 0), ("c1_41_p2", "1,0,0", 63), ("c1_41_p2", "2,0,0", 0), ("p5_seq3", "1,0,0", 0),
+    ("c1_41_p2", "1,0,0", 0), ("c1_41_p2", "1,0,0", 127), ("c1_41_p2", "2,0,0", 0), ("p5_seq3", "1,0,0", 0),
     ("p5_seq3", "4,0,0", 0), ("p21_41", "2,0,0", 0), ("ties_int", "2,0,0", 0), ("mag_tiny", "2,0,0", 0),
     ("c2_41_b30", "1,0,3", 0), ("c2_41_b30", "9,0,2", 0), ("shape_100x37", "2,0,0", 0),
     ("c3_321_randn", "0,0,0", 0), ("c3_321_randn", "4,0,1", 16), ("c4_513_b4", "9,0,1", 0), ("c4_513_b4", "9,0,2", 0),
