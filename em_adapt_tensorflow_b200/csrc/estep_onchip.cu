@@ -2276,18 +2276,31 @@ __global__ void __launch_bounds__(NT_ + NPW * 32, 1) estep_onchip_kernel(const _
                     if (bias != 0.f) {
                         // fold: x += bias (weaklabel.cpp:90-92), E = max(E, x) (:94-99)
                         uint32_t gall = 0u, gnew = 0u, znew = 0u;
-                        for_each_quad<NT_, QPT>(c, ta, [&](int kq, int q, float4 x) {
-                            const float4 xn = make_float4(__fadd_rn(x.x, bias), __fadd_rn(x.y, bias), __fadd_rn(x.z, bias), __fadd_rn(x.w, bias));
-                            tm_st4(ta + 4 * kq, xn);                  // warp-collective (quads beyond the tile stay -inf)
-                            if (q >= c.TQ) return;
-                            float4 *Ep = reinterpret_cast<float4 *>(c.sE() + 4 * q);
-                            float4 E = *Ep;
-                            gall += (xn.x > E.x) + (xn.y > E.y) + (xn.z > E.z) + (xn.w > E.w);
-                            gnew += (xn.x > E.x && x.x < E.x) + (xn.y > E.y && x.y < E.y) + (xn.z > E.z && x.z < E.z) + (xn.w > E.w && x.w < E.w);
-                            znew += (xn.x >= E.x) + (xn.y >= E.y) + (xn.z >= E.z) + (xn.w >= E.w);
-                            E.x = fmaxf(E.x, xn.x); E.y = fmaxf(E.y, xn.y); E.z = fmaxf(E.z, xn.z); E.w = fmaxf(E.w, xn.w);
-                            *Ep = E;
-                        });
+                        if (track_zeros) {
+                            for_each_quad<NT_, QPT>(c, ta, [&](int kq, int q, float4 x) {
+                                const float4 xn = make_float4(__fadd_rn(x.x, bias), __fadd_rn(x.y, bias), __fadd_rn(x.z, bias), __fadd_rn(x.w, bias));
+                                tm_st4(ta + 4 * kq, xn);                  // warp-collective (quads beyond the tile stay -inf)
+                                if (q >= c.TQ) return;
+                                float4 *Ep = reinterpret_cast<float4 *>(c.sE() + 4 * q);
+                                float4 E = *Ep;
+                                gall += (xn.x > E.x) + (xn.y > E.y) + (xn.z > E.z) + (xn.w > E.w);
+                                gnew += (xn.x > E.x && x.x < E.x) + (xn.y > E.y && x.y < E.y) + (xn.z > E.z && x.z < E.z) + (xn.w > E.w && x.w < E.w);
+                                znew += (xn.x >= E.x) + (xn.y >= E.y) + (xn.z >= E.z) + (xn.w >= E.w);
+                                E.x = fmaxf(E.x, xn.x); E.y = fmaxf(E.y, xn.y); E.z = fmaxf(E.z, xn.z); E.w = fmaxf(E.w, xn.w);
+                                *Ep = E;
+                            });
+                        } else {
+                            // every step of this image selects anyway: no zero-margin counts to maintain
+                            for_each_quad<NT_, QPT>(c, ta, [&](int kq, int q, float4 x) {
+                                const float4 xn = make_float4(__fadd_rn(x.x, bias), __fadd_rn(x.y, bias), __fadd_rn(x.z, bias), __fadd_rn(x.w, bias));
+                                tm_st4(ta + 4 * kq, xn);
+                                if (q >= c.TQ) return;
+                                float4 *Ep = reinterpret_cast<float4 *>(c.sE() + 4 * q);
+                                float4 E = *Ep;
+                                E.x = fmaxf(E.x, xn.x); E.y = fmaxf(E.y, xn.y); E.z = fmaxf(E.z, xn.z); E.w = fmaxf(E.w, xn.w);
+                                *Ep = E;
+                            });
+                        }
                         tm_wait_st();
                         SELP(c, 6);
                         if (sl) c.dirty1 = true; else c.dirty0 = true;
