@@ -53,7 +53,7 @@ constexpr int MAXG = OC_MAXG;
 constexpr int NPW = 4;                  // producer warps per CTA
 constexpr int NST = 8;                  // stages of the staging ring (a multiple of NPW: a stage always belongs
                                         // to the same warp, which then sees its mbarrier phases in order)
-constexpr int STAGE_BYTES = 7168;
+constexpr int STAGE_BYTES = 8096;              // 96 pixels of 21 classes + 32 bytes of alignment slack: three full rounds of 32 lanes
 constexpr int EAGER_P = 4;              // planes whose zero counts are formed by the producers
 constexpr int DIG_SEG = 8;              // segments of a pushed digest
 constexpr int DIG_CROSS = 3;            // binade-crossing chunks whose terms travel with the digest
