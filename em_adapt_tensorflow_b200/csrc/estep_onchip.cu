@@ -470,7 +470,7 @@ __device__ __forceinline__ double block_excl_scan_f64(Cx<NT_> &c, double v, doub
 // A LIGHT image: one or two present classes, both planes resident in tensor memory for the whole image, no
 // suppressed absent maximum to keep (that needs the whole pixel): see prod_chunk_light / plane_load_light.
 __device__ __forceinline__ bool image_is_light(const EStepParams &p, int P, int cls0) {
-    return p.light_ok && P <= 2 && !(P == 1 && P < p.C && cls0 != 0) && !(p.flags & OC_F_NO_RESIDENT) && !p.up_src;
+    return p.light_ok && P <= 2 && !(P == 1 && P < p.C && cls0 != 0) && !(p.flags & OC_F_NO_RESIDENT);
 }
 
 struct Prod {
@@ -750,7 +750,7 @@ __device__ __forceinline__ void prod_upsampled_loop(const EStepParams &p, const 
 // Same operations on the same operands as up_value(): the same bits.
 __device__ __forceinline__ void prod_upsampled_separable(const EStepParams &p, const float *src, float *hrow, int r0, int nrows, int pw,
                                                          int lane, int base, int n_t, const uint8_t *pl, int P, float *planes,
-                                                         ProdStats &st) {
+                                                         bool light, ProdStats &st) {
     const int W = p.up_W, w = p.up_w, C = p.C;
     const int total = nrows * P * W;
     for (int idx = pw * 32 + lane; idx < total; idx += NPW * 32) {
@@ -785,6 +785,7 @@ __device__ __forceinline__ void prod_upsampled_separable(const EStepParams &p, c
             else if (v == E) { at++; if (k < 4) eq |= 1u << k; }
             if (v < mn) mn = v;
         }
+        if (light) continue;                       // LIGHT image: E0 and the statistics are formed by the compute threads
         __stcg(e0pl + i, E);
         st.zc0 += eq & 1u; st.zc1 += (eq >> 1) & 1u; st.zc2 += (eq >> 2) & 1u; st.zc3 += (eq >> 3) & 1u;
         st.ties += (at >= 2u) ? 1u : 0u;
@@ -804,7 +805,8 @@ __device__ __noinline__ void prod_upsampled(const EStepParams *pp, int b, int pw
         const int r0 = (int)__fmul_rn((float)ya, p.up_sy), r1 = min((int)__fmul_rn((float)yb, p.up_sy) + 1, p.up_h - 1);
         const int nfl = (r1 - r0 + 1) * p.up_w * p.C;
         if (!need_abs && (size_t)(r1 - r0 + 1) * P * p.up_W * sizeof(float) <= (size_t)NST * STAGE_BYTES) {
-            prod_upsampled_separable(p, src, staging, r0, r1 - r0 + 1, pw, lane, base, n_t, pl, P, planes, st);
+            prod_upsampled_separable(p, src, staging, r0, r1 - r0 + 1, pw, lane, base, n_t, pl, P, planes,
+                                     image_is_light(p, P, pl[0]), st);
         } else if ((size_t)nfl * sizeof(float) <= (size_t)NST * STAGE_BYTES) {
             const float *g = src + (size_t)r0 * p.up_w * p.C;
             for (int f = pw * 32 + lane; f < nfl; f += NPW * 32) staging[f] = __ldg(g + f);
