@@ -31,6 +31,16 @@
 //     image (E0 is still in shared memory) and costs no cluster round trip of its own.
 //   * LABELS IN FLOAT: argmax over the final scores; only pixels whose best two scores are within the
 //     rounding distance of the re-centring shift (weaklabel.cpp:108-112) take the exact double path.
+//   * LABELS-ONLY MODE: the shift is bounded WITHOUT the two order-exact sums, every provably safe pixel is
+//     labelled at once (pass A, out through shared memory in 16-byte stores), and the sums are formed only for
+//     the images in which a pixel stays open (pass B decides those exactly).
+// and on the producer side:
+//   * a LIGHT path for label sets of one or two classes (both planes stay in tensor memory): the producers only
+//     de-interleave, E0 and the statistics are formed by the compute threads while the planes go into TMEM;
+//   * ring stages of 96 pixels (three full rounds of 32 lanes), every interior chunk ONE bulk copy of the
+//     16-byte-aligned span around it (cp.async head / tail floats only at the two ends of the tensor);
+//   * FUSED BILINEAR UP-SAMPLING (network.py:40): with EStepParams::up_src the producers stream nothing and
+//     interpolate the present classes from the low-resolution tensor (prod_upsampled, upsample.cuh).
 #include <float.h>
 #include <math.h>
 #include "estep_kernel.cuh"
