@@ -1922,6 +1922,10 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
     const int cls0 = r0 >= 0 ? c.msp()->plist[r0] : 0, cls1 = r1 >= 0 ? c.msp()->plist[r1] : 0;
     const bool two_resident = (c.P == 2 && r0 >= 0 && r1 >= 0 && r0 != r1);
     unsigned long long unsure = 0ull;
+    // one loop per case (both planes resident / the general one): inside ONE loop the two bodies shared a register
+    // allocation and the loop spilled around every quad
+    auto rounds = [&](auto tag) {
+    constexpr bool TWO = decltype(tag)::value != 0;
 #pragma unroll 1
     for (int k = 0; k < QPT; k++) {
         // tcgen05.ld is warp-collective: both slots are read by every lane for every k
@@ -1932,7 +1936,7 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
         const float a0[4] = {s0v.x, s0v.y, s0v.z, s0v.w};
         const float a1[4] = {s1v.x, s1v.y, s1v.z, s1v.w};
         uint32_t lab4 = 0u, un4 = 0u;
-        if (two_resident) {
+        if (TWO) {
             // both planes in tensor memory: the first maximum in CLASS order, safe unless the two scores
             // are distinct and within the guard, or equal (then an absent class may tie after rounding)
             const int lo_cls = r0 < r1 ? cls0 : cls1, hi_cls = r0 < r1 ? cls1 : cls0;
@@ -2003,6 +2007,8 @@ __device__ __forceinline__ unsigned long long labels_pass_a(Cx<NT_> &c, float as
         }
         unsure |= (unsigned long long)un4 << (4 * k);
     }
+    };
+    if (two_resident) rounds(IntTag<1>()); else rounds(IntTag<0>());
     return unsure;
 }
 
